@@ -1,0 +1,170 @@
+/* rtb200.h — C ABI of the B200-native path-tracing backend (librtb200.so).
+ *
+ * Drop-in boundary for the render hot path of semicolonTransistor/rust-ray-tracing.  Each entry point cites the
+ * reference interface it replaces (paths relative to the reference repository root).  Plain pointers and sizes
+ * only; the library owns all device memory; nothing aborts across this boundary — every call returns
+ * RTB200_OK (0) or a negative error code and rtb200_last_error() holds a message.
+ *
+ * There is no CPU fallback: every compute entry point needs a CUDA device and fails with
+ * RTB200_ERR_CUDA when none is usable.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTB200_OK 0
+#define RTB200_ERR_INVALID (-1) /* bad argument (null pointer, non-positive size, unknown material, ...) */
+#define RTB200_ERR_CUDA (-2)    /* CUDA runtime error, or no usable device */
+#define RTB200_ERR_STATE (-3)   /* call order (e.g. render before upload_scene) */
+
+/* Material kinds — mirror of the three `impl Material` types, src/materials.rs:43-147. */
+#define RTB200_LAMBERTIAN 0 /* src/materials.rs:43-69  */
+#define RTB200_METAL 1      /* src/materials.rs:73-107 */
+#define RTB200_DIELECTRIC 2 /* src/materials.rs:111-155 */
+
+/* Mirror of the reference's material structs (src/materials.rs:45, :75-76, :113-114).
+ * `param` is Metal::fuzzy_factor (clamped to <= 1.0 on upload exactly as Metal::new does, :79-88)
+ * or Dielectric::index_of_refraction.  `hollow` is Dielectric::hollow. */
+typedef struct rtb200_material {
+    int32_t kind;
+    int32_t hollow;
+    double albedo[3];
+    double param;
+} rtb200_material;
+
+/* Mirror of Sphere { center, radius, material } (src/objects.rs:203-209).  `material` indexes
+ * rtb200_scene::materials (the reference holds an Arc<dyn Material>). */
+typedef struct rtb200_sphere {
+    double center[3];
+    double radius;
+    int32_t material;
+    int32_t _pad;
+} rtb200_sphere;
+
+/* Mirror of Scene { objects: Vec<Object> } (src/ray_tracing.rs:100-104).  Object order is significant:
+ * the closest-hit tie-break is "last object wins" (src/objects.rs:141). */
+typedef struct rtb200_scene {
+    const rtb200_sphere* spheres;
+    int32_t n_spheres;
+    const rtb200_material* materials;
+    int32_t n_materials;
+} rtb200_scene;
+
+/* Mirror of Camera (src/ray_tracing.rs:15-24): the eight derived quantities, in f64. */
+typedef struct rtb200_camera {
+    int32_t image_width;
+    int32_t image_height;
+    double center[3];
+    double viewport_upper_left_corner[3];
+    double viewport_u[3];
+    double viewport_v[3];
+    double defocus_u[3];
+    double defocus_v[3];
+} rtb200_camera;
+
+/* Arguments of Renderer::render (src/renderer.rs:38-40) plus what the reference hard-codes or lacks:
+ * the sample stream seed (the reference is OS-seeded, src/ray_tracing.rs:78), and the shard of the
+ * job this call renders (the reference shards by 128x128 tile over threads, src/renderer.rs:254-266). */
+typedef struct rtb200_params {
+    int32_t max_bounces;       /* render(max_bounces, ...)        */
+    int32_t samples_per_pixel; /* render(..., samples_per_pixel)  — divisor of the final mean */
+    uint64_t seed;             /* Philox key                                                   */
+    int32_t sample_begin;      /* this call traces samples [sample_begin, sample_end) of each pixel */
+    int32_t sample_end;        /*   (0, samples_per_pixel for the whole job)                   */
+    int32_t row_begin;         /* and image rows [row_begin, row_end)  (0, image_height)       */
+    int32_t row_end;
+    int32_t flags;             /* RTB200_FLAG_* */
+    int32_t _pad;
+} rtb200_params;
+
+#define RTB200_FLAG_NONE 0
+
+/* Mirror of RenderStat (src/renderer.rs:11-34) plus the counters the metric needs. */
+typedef struct rtb200_stats {
+    double seconds;             /* RenderStat::duration — wall time of the call                      */
+    uint64_t pixels_rendered;   /* RenderStat::pixels_rendered                                       */
+    double pixels_per_second;   /* RenderStat::pixels_per_second                                     */
+    uint64_t paths;             /* (pixel, sample) paths traced                                      */
+    uint64_t segments;          /* rays cast (one closest-hit sweep each)                            */
+    uint64_t sphere_tests;      /* segments * n_spheres (brute force, src/ray_tracing.rs:399-401)    */
+    double trace_ms;            /* device time of the trace kernel (CUDA events)                     */
+    double resolve_ms;          /* device time of the resolve kernel                                 */
+    double h2d_ms, d2h_ms;      /* host<->device copies inside the call                              */
+} rtb200_stats;
+
+typedef struct rtb200_ctx rtb200_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------------------------ */
+
+/* TileRenderer::new (src/renderer.rs:232-240): makes a renderer.  Binds CUDA device `device`. */
+int rtb200_create(int32_t device, rtb200_ctx** out);
+void rtb200_destroy(rtb200_ctx* ctx);
+const char* rtb200_last_error(void);
+/* Library / device facts: SM count, max SM clock (kHz), compiled arch.  Any pointer may be null. */
+int rtb200_device_info(rtb200_ctx* ctx, int32_t* sm_count, int32_t* sm_clock_khz, int32_t* cc_major, int32_t* cc_minor);
+
+/* Camera::new (src/ray_tracing.rs:27-62), evaluated in f64 on the host.  Pure host arithmetic (no device). */
+int rtb200_camera_init(rtb200_camera* out, int32_t image_width, int32_t image_height, double focal_length,
+                       double view_angle_deg, const double center[3], const double look_at[3], const double up[3],
+                       double defocus_angle_deg);
+
+/* Scene::from_list (src/ray_tracing.rs:222-224): flattens the scene to the device layout
+ * (float4 {cx,cy,cz,r*r} per sphere + per-sphere material records) and uploads it. */
+int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene);
+
+/* ---- the render path, host buffers (the reference-facing call) ------------------------------------------- */
+
+/* Renderer::render (src/renderer.rs:38-40, impl :244-387): trace + resolve, host buffers in and out.
+ * rgb8_out: image_width*image_height*3 bytes, row-major, row 0 = top (RgbImage layout, :376-384); may be null.
+ * linear_rgba_out: image_width*image_height*4 floats, the un-quantised per-pixel SUM over the traced samples
+ * (r,g,b, sample count); may be null. */
+int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, uint8_t* rgb8_out,
+                  float* linear_rgba_out, rtb200_stats* stats);
+
+/* Scene sweep = Object::hit_packed over all objects + PackedHitRecords::update
+ * (src/ray_tracing.rs:397-403, src/objects.rs:249-290, :140-155) for a batch of rays, host buffers.
+ * rays: SoA float arrays of length n.  enabled: PackedRays::enabled lane mask (src/ray.rs:41), may be null (= all).
+ * hit_index[i] = object index of the closest near-root hit or -1; hit_t[i] = its t, +inf on a miss. */
+int rtb200_intersect_batch(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx,
+                           const float* dy, const float* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index,
+                           float* hit_t);
+
+/* ---- the same kernels on device-resident buffers (for callers that own device memory and streams) -------- */
+
+/* Trace kernel only: accumulates the per-pixel linear SUM of the shard named by `params` into accum_dev
+ * (image_width*image_height float4 {r,g,b,n_samples}, device memory).  Rows outside [row_begin,row_end) are
+ * left untouched.  `stream` is a cudaStream_t (null = default stream).  Asynchronous. */
+int rtb200_trace_device(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev,
+                        void* stream);
+
+/* Resolve kernel: sum/spp + Color::to_u8_array (src/renderer.rs:161-163, src/color.rs:54-64).
+ * accum_dev: n_pixels float4; rgb8_dev: n_pixels*3 bytes (device).  Asynchronous. */
+int rtb200_resolve_device(rtb200_ctx* ctx, const void* accum_dev, int64_t n_pixels, int32_t samples_per_pixel,
+                          void* rgb8_dev, void* stream);
+
+/* intersect_batch on device pointers.  Asynchronous. */
+int rtb200_intersect_batch_device(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx,
+                                  const float* dy, const float* dz, const uint8_t* enabled, int64_t n,
+                                  int32_t* hit_index, float* hit_t, void* stream);
+
+/* Device counters of the last trace on this context (valid after the stream has been synchronised). */
+int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
+
+/* Number of kernel launches this context has issued since creation (trace, resolve, intersect, probe). */
+int64_t rtb200_launch_count(rtb200_ctx* ctx);
+
+/* K0: measures sustained FP32 FMA throughput (dependent-free FFMA chains on every SM) — the roofline
+ * denominator for this path (the driver's MEASURED_PEAKS.json holds only HBM and BF16 figures).
+ * Returns TFLOP/s (FMA = 2 FLOP) in *tflops and the kernel's device time in *ms. */
+int rtb200_fp32_peak(rtb200_ctx* ctx, int32_t iters, double* tflops, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTB200_H */

@@ -1,0 +1,95 @@
+"""ctypes binding of include/rtb200.h (librtb200.so).
+
+The library is the product: if it is missing or does not load, importing this module raises — there is no
+Python or CPU fallback for any compute entry point.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtb200.so")
+
+OK, ERR_INVALID, ERR_CUDA, ERR_STATE = 0, -1, -2, -3
+LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
+
+
+class Material(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("hollow", C.c_int32), ("albedo", C.c_double * 3), ("param", C.c_double)]
+
+
+class Sphere(C.Structure):
+    _fields_ = [("center", C.c_double * 3), ("radius", C.c_double), ("material", C.c_int32), ("_pad", C.c_int32)]
+
+
+class Scene(C.Structure):
+    _fields_ = [("spheres", C.POINTER(Sphere)), ("n_spheres", C.c_int32), ("materials", C.POINTER(Material)),
+                ("n_materials", C.c_int32)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("image_width", C.c_int32), ("image_height", C.c_int32), ("center", C.c_double * 3),
+                ("viewport_upper_left_corner", C.c_double * 3), ("viewport_u", C.c_double * 3),
+                ("viewport_v", C.c_double * 3), ("defocus_u", C.c_double * 3), ("defocus_v", C.c_double * 3)]
+
+
+class Params(C.Structure):
+    _fields_ = [("max_bounces", C.c_int32), ("samples_per_pixel", C.c_int32), ("seed", C.c_uint64),
+                ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("row_begin", C.c_int32),
+                ("row_end", C.c_int32), ("flags", C.c_int32), ("_pad", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("seconds", C.c_double), ("pixels_rendered", C.c_uint64), ("pixels_per_second", C.c_double),
+                ("paths", C.c_uint64), ("segments", C.c_uint64), ("sphere_tests", C.c_uint64),
+                ("trace_ms", C.c_double), ("resolve_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double)]
+
+
+# every symbol include/rtb200.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+_F = C.POINTER(C.c_float)
+SYMBOLS = {
+    "rtb200_create": (C.c_int, [C.c_int32, C.POINTER(_P)]),
+    "rtb200_destroy": (None, [_P]),
+    "rtb200_last_error": (C.c_char_p, []),
+    "rtb200_device_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "rtb200_camera_init": (C.c_int, [C.POINTER(Camera), C.c_int32, C.c_int32, C.c_double, C.c_double,
+                                     C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double]),
+    "rtb200_upload_scene": (C.c_int, [_P, C.POINTER(Scene)]),
+    "rtb200_render": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P, C.POINTER(Stats)]),
+    "rtb200_intersect_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P]),
+    "rtb200_trace_device": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P]),
+    "rtb200_resolve_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
+    "rtb200_intersect_batch_device": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
+    "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "rtb200_launch_count": (C.c_int64, [_P]),
+    "rtb200_fp32_peak": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+}
+
+
+def load(path: str = LIB_PATH) -> C.CDLL:
+    if not os.path.exists(path):
+        raise ImportError(f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(rtb200 has no CPU fallback)")
+    lib = C.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)   # AttributeError if the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = load()
+
+
+class Rtb200Error(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"rtb200 error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+def check(rc: int) -> None:
+    if rc != OK:
+        raise Rtb200Error(rc, (lib.rtb200_last_error() or b"").decode("utf-8", "replace"))

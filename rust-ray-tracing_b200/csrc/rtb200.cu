@@ -1,0 +1,455 @@
+// rtb200.cu — C ABI (include/rtb200.h) over the sm_100a kernels in rt_kernels.cuh.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -Xcompiler -fPIC -shared
+// There is no CPU path in this file: every compute entry point launches a kernel or fails.
+#include "../../include/rtb200.h"
+#include "rt_kernels.cuh"
+
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define CU_TRY(expr)                                                                                           \
+    do {                                                                                                       \
+        cudaError_t _e = (expr);                                                                               \
+        if (_e != cudaSuccess)                                                                                 \
+            return fail(RTB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));                   \
+    } while (0)
+
+constexpr int SMALL_THREADS = 256, SMALL_BLOCKS = 4;   // scenes whose staging fits four CTAs per SM
+constexpr int LARGE_THREADS = 1024, LARGE_BLOCKS = 1;  // one CTA per SM, up to ~11k spheres resident in shared memory
+
+size_t trace_smem_bytes(int padded, int threads) { return (size_t)padded * sizeof(float4) + (size_t)rtb::LIST_CAP * threads * sizeof(uint2); }
+
+}  // namespace
+
+struct rtb200_ctx {
+    int device = 0;
+    cudaDeviceProp prop{};
+    // scene
+    float4* d_spheres = nullptr;
+    float4* d_mat = nullptr;
+    int* d_mat_kind = nullptr;
+    int n_spheres = 0;
+    // counters: [0] paths [1] segments [2] work counter
+    unsigned long long* d_counters = nullptr;
+    // render-call scratch
+    float4* d_accum = nullptr; size_t accum_pixels = 0;
+    uint8_t* d_rgb8 = nullptr; size_t rgb8_bytes = 0;
+    float4* d_partial = nullptr; size_t partial_elems = 0;
+    void* d_rays = nullptr; size_t rays_bytes = 0;
+    float* d_probe = nullptr;
+    cudaEvent_t ev[4]{};
+    int64_t launches = 0;
+    size_t max_optin_smem = 0;
+    bool attrs_set = false;
+};
+
+namespace {
+
+int ensure(void** p, size_t* have, size_t want) {
+    if (*have >= want && *p) return RTB200_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *have = 0;
+    CU_TRY(cudaMalloc(p, want));
+    *have = want;
+    return RTB200_OK;
+}
+
+rtb::f3 to_f3(const double v[3]) { return rtb::f3{(float)v[0], (float)v[1], (float)v[2]}; }
+
+rtb::DeviceCamera device_camera(const rtb200_camera& c) {
+    rtb::DeviceCamera d;
+    d.width = c.image_width; d.height = c.image_height;
+    d.center = to_f3(c.center); d.ulc = to_f3(c.viewport_upper_left_corner);
+    d.viewport_u = to_f3(c.viewport_u); d.viewport_v = to_f3(c.viewport_v);
+    d.defocus_u = to_f3(c.defocus_u); d.defocus_v = to_f3(c.defocus_v);
+    auto nz = [](rtb::f3 a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f; };
+    d.defocus_enabled = (nz(d.defocus_u) || nz(d.defocus_v)) ? 1 : 0;
+    return d;
+}
+
+int validate_params(const rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p) {
+    if (!ctx || !cam || !p) return fail(RTB200_ERR_INVALID, "null argument");
+    if (!ctx->d_spheres) return fail(RTB200_ERR_STATE, "no scene uploaded (call rtb200_upload_scene first)");
+    if (cam->image_width <= 0 || cam->image_height <= 0) return fail(RTB200_ERR_INVALID, "image size must be positive");
+    if ((int64_t)cam->image_width * cam->image_height > (int64_t)1 << 31) return fail(RTB200_ERR_INVALID, "image too large");
+    if (p->max_bounces < 0) return fail(RTB200_ERR_INVALID, "max_bounces must be >= 0");
+    if (p->samples_per_pixel <= 0) return fail(RTB200_ERR_INVALID, "samples_per_pixel must be positive");
+    if (p->sample_begin < 0 || p->sample_end < p->sample_begin) return fail(RTB200_ERR_INVALID, "bad sample range");
+    if (p->row_begin < 0 || p->row_end < p->row_begin || p->row_end > cam->image_height) return fail(RTB200_ERR_INVALID, "bad row range");
+    return RTB200_OK;
+}
+
+// Chooses the number of sample splits K so that the persistent grid has many more work items than lanes
+// (tail balance) while each item keeps several samples (register-resident sum).
+int choose_splits(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
+    long long lanes = (long long)ctx->prop.multiProcessorCount * 1024;
+    long long want_items = lanes * 24;
+    long long k = (want_items + n_pix - 1) / (n_pix > 0 ? n_pix : 1);
+    long long kmax = n_samples / 4;
+    if (k > kmax) k = kmax;
+    if (k < 1) k = 1;
+    if (k > 64) k = 64;
+    return (int)k;
+}
+
+int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p, float4* accum, cudaStream_t st) {
+    const int W = cam->image_width;
+    const long long n_pix = (long long)(p->row_end - p->row_begin) * W;
+    CU_TRY(cudaMemsetAsync(ctx->d_counters, 0, 3 * sizeof(unsigned long long), st));
+    if (n_pix == 0) return RTB200_OK;
+    const int n_samples = p->sample_end - p->sample_begin;
+    rtb::TraceParams P;
+    P.cam = device_camera(*cam);
+    P.spheres = ctx->d_spheres; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
+    P.n_spheres = ctx->n_spheres;
+    P.padded = (ctx->n_spheres + rtb::SWEEP_BLOCK - 1) / rtb::SWEEP_BLOCK * rtb::SWEEP_BLOCK;
+    P.max_bounces = p->max_bounces;
+    P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
+    P.sample_begin = p->sample_begin; P.sample_end = p->sample_end;
+    P.row_begin = p->row_begin; P.row_end = p->row_end;
+    P.splits = choose_splits(ctx, n_pix, n_samples);
+    P.work_counter = ctx->d_counters + 2;
+    P.counters = ctx->d_counters;
+    if (P.splits > 1) {
+        size_t want = (size_t)P.splits * (size_t)n_pix;
+        if (ctx->partial_elems < want) {
+            if (ctx->d_partial) cudaFree(ctx->d_partial);
+            ctx->d_partial = nullptr; ctx->partial_elems = 0;
+            CU_TRY(cudaMalloc(&ctx->d_partial, want * sizeof(float4)));
+            ctx->partial_elems = want;
+        }
+        P.out = ctx->d_partial;
+    } else {
+        P.out = accum;
+    }
+    if (!ctx->attrs_set) {
+        CU_TRY(cudaFuncSetAttribute(rtb::k_trace_paths<SMALL_THREADS, SMALL_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(rtb::k_trace_paths<LARGE_THREADS, LARGE_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        ctx->attrs_set = true;
+    }
+    const int sms = ctx->prop.multiProcessorCount;
+    size_t smem_small = trace_smem_bytes(P.padded, SMALL_THREADS);
+    size_t smem_large = trace_smem_bytes(P.padded, LARGE_THREADS);
+    size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
+    if ((smem_small + 1024) * SMALL_BLOCKS <= per_sm) {
+        rtb::k_trace_paths<SMALL_THREADS, SMALL_BLOCKS><<<sms * SMALL_BLOCKS, SMALL_THREADS, smem_small, st>>>(P);
+    } else if (smem_large <= ctx->max_optin_smem) {
+        rtb::k_trace_paths<LARGE_THREADS, LARGE_BLOCKS><<<sms * LARGE_BLOCKS, LARGE_THREADS, smem_large, st>>>(P);
+    } else {
+        return fail(RTB200_ERR_INVALID, "scene too large for shared-memory staging (" + std::to_string(ctx->n_spheres) + " spheres)");
+    }
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    if (P.splits > 1) {
+        int blocks = (int)((n_pix + 255) / 256);
+        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, P.splits, n_pix, accum + (size_t)p->row_begin * W);
+        CU_TRY(cudaGetLastError());
+        ctx->launches++;
+    }
+    return RTB200_OK;
+}
+
+int launch_resolve(rtb200_ctx* ctx, const float4* accum, long long n_pix, int spp, uint8_t* rgb8, cudaStream_t st) {
+    if (n_pix <= 0) return RTB200_OK;
+    long long quads = (n_pix + 3) / 4;
+    int blocks = (int)((quads + 255) / 256);
+    rtb::k_resolve<<<blocks, 256, 0, st>>>(accum, n_pix, (float)spp, rgb8);
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    return RTB200_OK;
+}
+
+int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx, const float* dy,
+                     const float* dz, const uint8_t* enabled, long long n, int* idx, float* t, cudaStream_t st) {
+    if (n <= 0) return RTB200_OK;
+    const int threads = 256;
+    int padded_all = (ctx->n_spheres + rtb::SWEEP_BLOCK - 1) / rtb::SWEEP_BLOCK * rtb::SWEEP_BLOCK;
+    int tile = padded_all < 2048 ? padded_all : 2048;
+    if (tile < rtb::SWEEP_BLOCK) tile = rtb::SWEEP_BLOCK;
+    size_t smem = (size_t)tile * sizeof(float4) + (size_t)rtb::LIST_CAP * threads * sizeof(uint2);
+    static bool attr = false;
+    if (!attr) {
+        CU_TRY(cudaFuncSetAttribute(rtb::k_intersect_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        attr = true;
+    }
+    long long blocks = (n + threads - 1) / threads;
+    if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
+    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t);
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    return RTB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* rtb200_last_error(void) { return g_last_error.c_str(); }
+
+int rtb200_create(int32_t device, rtb200_ctx** out) {
+    if (!out) return fail(RTB200_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(RTB200_ERR_CUDA, std::string("no CUDA device available: ") + cudaGetErrorString(e) + " (rtb200 has no CPU fallback)");
+    if (device < 0 || device >= count) return fail(RTB200_ERR_INVALID, "device index out of range");
+    CU_TRY(cudaSetDevice(device));
+    rtb200_ctx* c = new rtb200_ctx();
+    c->device = device;
+    e = cudaGetDeviceProperties(&c->prop, device);
+    if (e != cudaSuccess) { delete c; return fail(RTB200_ERR_CUDA, cudaGetErrorString(e)); }
+    if (c->prop.major < 10) {
+        std::string msg = "device compute capability " + std::to_string(c->prop.major) + "." + std::to_string(c->prop.minor) + " < 10.0: this library carries sm_100a code only";
+        delete c;
+        return fail(RTB200_ERR_CUDA, msg);
+    }
+    c->max_optin_smem = c->prop.sharedMemPerBlockOptin;
+    e = cudaMalloc(&c->d_counters, 3 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(c->d_counters, 0, 3 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_probe, sizeof(float));
+    for (int i = 0; i < 4 && e == cudaSuccess; i++) e = cudaEventCreate(&c->ev[i]);
+    if (e != cudaSuccess) { rtb200_destroy(c); return fail(RTB200_ERR_CUDA, cudaGetErrorString(e)); }
+    *out = c;
+    return RTB200_OK;
+}
+
+void rtb200_destroy(rtb200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaFree(c->d_spheres); cudaFree(c->d_mat); cudaFree(c->d_mat_kind); cudaFree(c->d_counters);
+    cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
+    for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    delete c;
+}
+
+int rtb200_device_info(rtb200_ctx* ctx, int32_t* sm_count, int32_t* sm_clock_khz, int32_t* cc_major, int32_t* cc_minor) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (sm_count) *sm_count = ctx->prop.multiProcessorCount;
+    if (sm_clock_khz) *sm_clock_khz = ctx->prop.clockRate;
+    if (cc_major) *cc_major = ctx->prop.major;
+    if (cc_minor) *cc_minor = ctx->prop.minor;
+    return RTB200_OK;
+}
+
+// Camera::new, src/ray_tracing.rs:27-62 — f64 on the host, like the reference.
+int rtb200_camera_init(rtb200_camera* out, int32_t image_width, int32_t image_height, double focal_length, double view_angle_deg,
+                       const double center[3], const double look_at[3], const double up[3], double defocus_angle_deg) {
+    if (!out || !center || !look_at || !up) return fail(RTB200_ERR_INVALID, "null argument");
+    if (image_width <= 0 || image_height <= 0) return fail(RTB200_ERR_INVALID, "image size must be positive");
+    struct D3 { double x, y, z; };
+    auto sub = [](D3 a, D3 b) { return D3{a.x - b.x, a.y - b.y, a.z - b.z}; };
+    auto scale = [](D3 a, double s) { return D3{a.x * s, a.y * s, a.z * s}; };
+    auto divs = [](D3 a, double s) { return D3{a.x / s, a.y / s, a.z / s}; };
+    auto unit = [&](D3 a) { return divs(a, std::sqrt(a.x * a.x + a.y * a.y + a.z * a.z)); };
+    auto cross = [](D3 a, D3 b) { return D3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; };
+    const double deg = 3.14159265358979323846 / 180.0;
+    D3 c{center[0], center[1], center[2]}, la{look_at[0], look_at[1], look_at[2]}, upv{up[0], up[1], up[2]};
+    double aspect = (double)image_width / (double)image_height;
+    double vh = std::tan((view_angle_deg * deg) / 2.0) * focal_length * 2.0;
+    double vw = vh * aspect;
+    D3 dir = unit(sub(la, c));
+    D3 w{-dir.x, -dir.y, -dir.z};
+    D3 u = unit(cross(upv, w));
+    D3 v = cross(w, u);
+    D3 vu = scale(u, vw);
+    D3 vv = scale(D3{-v.x, -v.y, -v.z}, vh);
+    D3 ulc = sub(sub(sub(c, scale(w, focal_length)), divs(vu, 2.0)), divs(vv, 2.0));
+    double dr = focal_length * std::tan((defocus_angle_deg / 2.0) * deg);
+    D3 du = scale(u, dr), dv = scale(v, dr);
+    out->image_width = image_width; out->image_height = image_height;
+    auto put = [](double* dst, D3 a) { dst[0] = a.x; dst[1] = a.y; dst[2] = a.z; };
+    put(out->center, c); put(out->viewport_upper_left_corner, ulc); put(out->viewport_u, vu); put(out->viewport_v, vv);
+    put(out->defocus_u, du); put(out->defocus_v, dv);
+    return RTB200_OK;
+}
+
+int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
+    if (!ctx || !scene) return fail(RTB200_ERR_INVALID, "null argument");
+    if (scene->n_spheres < 0 || scene->n_materials < 0) return fail(RTB200_ERR_INVALID, "negative count");
+    if (scene->n_spheres > 0 && (!scene->spheres || !scene->materials)) return fail(RTB200_ERR_INVALID, "null scene arrays");
+    const int n = scene->n_spheres;
+    std::vector<float4> sph((size_t)(n > 0 ? n : 1)), mat((size_t)(n > 0 ? n : 1));
+    std::vector<int> kind((size_t)(n > 0 ? n : 1));
+    for (int i = 0; i < n; i++) {
+        const rtb200_sphere& s = scene->spheres[i];
+        if (s.material < 0 || s.material >= scene->n_materials)
+            return fail(RTB200_ERR_INVALID, "sphere " + std::to_string(i) + " names material " + std::to_string(s.material) + " which does not exist");
+        const rtb200_material& m = scene->materials[s.material];
+        float r = (float)s.radius;
+        sph[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], r * r);   // radius.powi(2), src/objects.rs:256
+        double param = m.param;
+        if (m.kind == RTB200_METAL) param = (param < 1.0) ? param : 1.0;                           // Metal::new, src/materials.rs:79-88
+        else if (m.kind != RTB200_LAMBERTIAN && m.kind != RTB200_DIELECTRIC)
+            return fail(RTB200_ERR_INVALID, "Unknown material type " + std::to_string(m.kind));     // src/materials.rs:31
+        mat[i] = make_float4((float)m.albedo[0], (float)m.albedo[1], (float)m.albedo[2], (float)param);
+        kind[i] = m.kind | ((m.kind == RTB200_DIELECTRIC && m.hollow) ? RTB_HOLLOW_BIT : 0);
+    }
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaFree(ctx->d_spheres); cudaFree(ctx->d_mat); cudaFree(ctx->d_mat_kind);
+    ctx->d_spheres = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
+    size_t cnt = (size_t)(n > 0 ? n : 1);
+    CU_TRY(cudaMalloc(&ctx->d_spheres, cnt * sizeof(float4)));
+    CU_TRY(cudaMalloc(&ctx->d_mat, cnt * sizeof(float4)));
+    CU_TRY(cudaMalloc(&ctx->d_mat_kind, cnt * sizeof(int)));
+    CU_TRY(cudaMemcpy(ctx->d_spheres, sph.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(ctx->d_mat, mat.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(ctx->d_mat_kind, kind.data(), cnt * sizeof(int), cudaMemcpyHostToDevice));
+    ctx->n_spheres = n;
+    return RTB200_OK;
+}
+
+int rtb200_trace_device(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev, void* stream) {
+    int rc = validate_params(ctx, camera, params);
+    if (rc) return rc;
+    if (!accum_dev) return fail(RTB200_ERR_INVALID, "accum_dev is null");
+    CU_TRY(cudaSetDevice(ctx->device));
+    return launch_trace(ctx, camera, params, static_cast<float4*>(accum_dev), static_cast<cudaStream_t>(stream));
+}
+
+int rtb200_resolve_device(rtb200_ctx* ctx, const void* accum_dev, int64_t n_pixels, int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+    if (!ctx || !accum_dev || !rgb8_dev) return fail(RTB200_ERR_INVALID, "null argument");
+    if (n_pixels < 0 || samples_per_pixel <= 0) return fail(RTB200_ERR_INVALID, "bad size");
+    CU_TRY(cudaSetDevice(ctx->device));
+    return launch_resolve(ctx, static_cast<const float4*>(accum_dev), n_pixels, samples_per_pixel, static_cast<uint8_t*>(rgb8_dev), static_cast<cudaStream_t>(stream));
+}
+
+int rtb200_intersect_batch_device(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx, const float* dy,
+                                  const float* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index, float* hit_t, void* stream) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (!ctx->d_spheres) return fail(RTB200_ERR_STATE, "no scene uploaded (call rtb200_upload_scene first)");
+    if (n < 0) return fail(RTB200_ERR_INVALID, "negative ray count");
+    if (n > 0 && (!ox || !oy || !oz || !dx || !dy || !dz || !hit_index || !hit_t)) return fail(RTB200_ERR_INVALID, "null ray buffer");
+    CU_TRY(cudaSetDevice(ctx->device));
+    return launch_intersect(ctx, ox, oy, oz, dx, dy, dz, enabled, n, hit_index, hit_t, static_cast<cudaStream_t>(stream));
+}
+
+int rtb200_intersect_batch(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx, const float* dy,
+                           const float* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index, float* hit_t) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (!ctx->d_spheres) return fail(RTB200_ERR_STATE, "no scene uploaded (call rtb200_upload_scene first)");
+    if (n < 0) return fail(RTB200_ERR_INVALID, "negative ray count");
+    if (n == 0) return RTB200_OK;
+    if (!ox || !oy || !oz || !dx || !dy || !dz || !hit_index || !hit_t) return fail(RTB200_ERR_INVALID, "null ray buffer");
+    CU_TRY(cudaSetDevice(ctx->device));
+    // layout of the device scratch: 6 float planes, idx plane, t plane, enabled bytes
+    size_t nn = (size_t)n;
+    size_t want = nn * (6 * sizeof(float) + sizeof(int) + sizeof(float) + 1);
+    int rc = ensure(&ctx->d_rays, &ctx->rays_bytes, want);
+    if (rc) return rc;
+    float* base = static_cast<float*>(ctx->d_rays);
+    const float* src[6] = {ox, oy, oz, dx, dy, dz};
+    for (int k = 0; k < 6; k++) CU_TRY(cudaMemcpyAsync(base + k * nn, src[k], nn * sizeof(float), cudaMemcpyHostToDevice, 0));
+    int* d_idx = reinterpret_cast<int*>(base + 6 * nn);
+    float* d_t = base + 7 * nn;
+    uint8_t* d_en = nullptr;
+    if (enabled) {
+        d_en = reinterpret_cast<uint8_t*>(base + 8 * nn);
+        CU_TRY(cudaMemcpyAsync(d_en, enabled, nn, cudaMemcpyHostToDevice, 0));
+    }
+    rc = launch_intersect(ctx, base, base + nn, base + 2 * nn, base + 3 * nn, base + 4 * nn, base + 5 * nn, d_en, n, d_idx, d_t, 0);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpyAsync(hit_index, d_idx, nn * sizeof(int), cudaMemcpyDeviceToHost, 0));
+    CU_TRY(cudaMemcpyAsync(hit_t, d_t, nn * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    CU_TRY(cudaStreamSynchronize(0));
+    return RTB200_OK;
+}
+
+int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, uint8_t* rgb8_out, float* linear_rgba_out,
+                  rtb200_stats* stats) {
+    int rc = validate_params(ctx, camera, params);
+    if (rc) return rc;
+    auto t0 = std::chrono::steady_clock::now();
+    CU_TRY(cudaSetDevice(ctx->device));
+    const size_t n_pix = (size_t)camera->image_width * camera->image_height;
+    {
+        void* p = ctx->d_accum; size_t have = ctx->accum_pixels * sizeof(float4);
+        rc = ensure(&p, &have, n_pix * sizeof(float4));
+        ctx->d_accum = static_cast<float4*>(p); ctx->accum_pixels = have / sizeof(float4);
+        if (rc) return rc;
+        p = ctx->d_rgb8; have = ctx->rgb8_bytes;
+        rc = ensure(&p, &have, n_pix * 3 + 16);
+        ctx->d_rgb8 = static_cast<uint8_t*>(p); ctx->rgb8_bytes = have;
+        if (rc) return rc;
+    }
+    cudaStream_t st = 0;
+    const bool full_rows = params->row_begin == 0 && params->row_end == camera->image_height;
+    if (!full_rows) CU_TRY(cudaMemsetAsync(ctx->d_accum, 0, n_pix * sizeof(float4), st));
+    CU_TRY(cudaEventRecord(ctx->ev[0], st));
+    rc = launch_trace(ctx, camera, params, ctx->d_accum, st);
+    if (rc) return rc;
+    CU_TRY(cudaEventRecord(ctx->ev[1], st));
+    rc = launch_resolve(ctx, ctx->d_accum, (long long)n_pix, params->samples_per_pixel, ctx->d_rgb8, st);
+    if (rc) return rc;
+    CU_TRY(cudaEventRecord(ctx->ev[2], st));
+    if (rgb8_out) CU_TRY(cudaMemcpyAsync(rgb8_out, ctx->d_rgb8, n_pix * 3, cudaMemcpyDeviceToHost, st));
+    if (linear_rgba_out) CU_TRY(cudaMemcpyAsync(linear_rgba_out, ctx->d_accum, n_pix * sizeof(float4), cudaMemcpyDeviceToHost, st));
+    CU_TRY(cudaEventRecord(ctx->ev[3], st));
+    CU_TRY(cudaStreamSynchronize(st));
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        unsigned long long cnt[3] = {0, 0, 0};
+        CU_TRY(cudaMemcpy(cnt, ctx->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); stats->trace_ms = ms;
+        CU_TRY(cudaEventElapsedTime(&ms, ctx->ev[1], ctx->ev[2])); stats->resolve_ms = ms;
+        CU_TRY(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3])); stats->d2h_ms = ms;
+        stats->paths = cnt[0]; stats->segments = cnt[1];
+        stats->sphere_tests = cnt[1] * (unsigned long long)ctx->n_spheres;
+        stats->pixels_rendered = (uint64_t)(params->row_end - params->row_begin) * camera->image_width;   // RenderStat::new, src/renderer.rs:385
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        stats->pixels_per_second = stats->seconds > 0 ? (double)stats->pixels_rendered / stats->seconds : 0.0;
+    }
+    return RTB200_OK;
+}
+
+int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    CU_TRY(cudaSetDevice(ctx->device));
+    unsigned long long cnt[2] = {0, 0};
+    CU_TRY(cudaMemcpy(cnt, ctx->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+    if (paths) *paths = cnt[0];
+    if (segments) *segments = cnt[1];
+    return RTB200_OK;
+}
+
+int64_t rtb200_launch_count(rtb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int rtb200_fp32_peak(rtb200_ctx* ctx, int32_t iters, double* tflops, double* ms_out) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (iters <= 0) iters = 2000;
+    CU_TRY(cudaSetDevice(ctx->device));
+    const int grid = ctx->prop.multiProcessorCount * 2;
+    rtb::k_fp32_peak<<<grid, 1024>>>(ctx->d_probe, 64, 1.0f);   // warm-up
+    CU_TRY(cudaGetLastError());
+    float best = 1e30f;
+    for (int r = 0; r < 3; r++) {
+        CU_TRY(cudaEventRecord(ctx->ev[0], 0));
+        rtb::k_fp32_peak<<<grid, 1024>>>(ctx->d_probe, iters, 1.0f);
+        CU_TRY(cudaEventRecord(ctx->ev[1], 0));
+        CU_TRY(cudaEventSynchronize(ctx->ev[1]));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1]));
+        if (ms < best) best = ms;
+    }
+    ctx->launches += 4;
+    double flop = 2.0 * 8.0 * 16.0 * (double)iters * 1024.0 * (double)grid;
+    if (tflops) *tflops = flop / ((double)best * 1e-3) * 1e-12;
+    if (ms_out) *ms_out = best;
+    return RTB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,154 @@
+"""Renderer — Python mirror of the reference's L2 boundary (src/renderer.rs).
+
+`Renderer.render(max_bounces, samples_per_pixel, scene, camera) -> (image, RenderStat)` is the reference's trait
+(src/renderer.rs:38-40); `CudaRenderer` is the B200 implementation that stands where `TileRenderer` stands
+(:232-240, :244-387).  Every call goes through the C ABI in include/rtb200.h; nothing here computes pixels.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import numpy as np
+
+from . import _abi
+from .scene import Camera, Scene
+
+
+@dataclass
+class RenderStat:
+    """RenderStat, src/renderer.rs:11-34, plus the counters the throughput metric needs."""
+    duration: float
+    pixels_rendered: int
+    pixels_per_second: float
+    paths: int = 0
+    segments: int = 0
+    sphere_tests: int = 0
+    trace_ms: float = 0.0
+    resolve_ms: float = 0.0
+    d2h_ms: float = 0.0
+
+
+class Renderer:
+    """trait Renderer, src/renderer.rs:38-40."""
+
+    def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera) -> Tuple[np.ndarray, RenderStat]:
+        raise NotImplementedError
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class CudaRenderer(Renderer):
+    """The sm_100a backend behind the reference's Renderer boundary.
+
+    `TileRenderer::new(num_threads, block_size)` (src/renderer.rs:232-240) picks threads and tile size; here the
+    equivalents are the CUDA device and the Philox seed of the sample stream.
+    """
+
+    def __init__(self, device: int = 0, seed: int = 1):
+        self._ctx = C.c_void_p()
+        _abi.check(_abi.lib.rtb200_create(int(device), C.byref(self._ctx)))
+        self.device = int(device)
+        self.seed = int(seed)
+        self._scene_id = None
+        self._keep = None
+
+    def close(self) -> None:
+        if getattr(self, "_ctx", None) is not None and self._ctx:
+            _abi.lib.rtb200_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- facts -------------------------------------------------------------------------------------------
+    def device_info(self) -> dict:
+        sm, khz, mj, mn = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        _abi.check(_abi.lib.rtb200_device_info(self._ctx, C.byref(sm), C.byref(khz), C.byref(mj), C.byref(mn)))
+        return {"sm_count": sm.value, "sm_clock_khz": khz.value, "cc": (mj.value, mn.value)}
+
+    def launch_count(self) -> int:
+        return int(_abi.lib.rtb200_launch_count(self._ctx))
+
+    def fp32_peak(self, iters: int = 2000) -> Tuple[float, float]:
+        """(TFLOP/s, ms) of the K0 FFMA probe."""
+        tf, ms = C.c_double(), C.c_double()
+        _abi.check(_abi.lib.rtb200_fp32_peak(self._ctx, int(iters), C.byref(tf), C.byref(ms)))
+        return tf.value, ms.value
+
+    # ---- scene ---------------------------------------------------------------------------------------------
+    def upload_scene(self, scene: Scene) -> None:
+        sc, keep = scene.to_abi()
+        _abi.check(_abi.lib.rtb200_upload_scene(self._ctx, C.byref(sc)))
+        self._scene_id = id(scene)
+        self._keep = keep
+        self.n_spheres = len(scene)
+
+    def _params(self, max_bounces, spp, camera, sample_range, row_range) -> _abi.Params:
+        s0, s1 = sample_range if sample_range is not None else (0, spp)
+        r0, r1 = row_range if row_range is not None else (0, camera.image_height())
+        return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), 0, 0)
+
+    # ---- Renderer::render -------------------------------------------------------------------------------------
+    def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera, *, want_linear: bool = False,
+               sample_range=None, row_range=None):
+        """Renderer::render (src/renderer.rs:38-40).  Returns (image[H,W,3] uint8, RenderStat); with want_linear=True
+        returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat)."""
+        if self._scene_id != id(scene):
+            self.upload_scene(scene)
+        W, H = camera.image_width(), camera.image_height()
+        img = np.empty((H, W, 3), dtype=np.uint8)
+        lin = np.empty((H, W, 4), dtype=np.float32) if want_linear else None
+        st = _abi.Stats()
+        p = self._params(max_bounces, samples_per_pixel, camera, sample_range, row_range)
+        _abi.check(_abi.lib.rtb200_render(self._ctx, C.byref(camera.abi), C.byref(p), _ptr(img), _ptr(lin), C.byref(st)))
+        stat = RenderStat(st.seconds, st.pixels_rendered, st.pixels_per_second, st.paths, st.segments, st.sphere_tests,
+                          st.trace_ms, st.resolve_ms, st.d2h_ms)
+        return (img, lin, stat) if want_linear else (img, stat)
+
+    # ---- the sweep alone (Object::hit_packed over the scene) --------------------------------------------------
+    def intersect_batch(self, scene: Scene, origins: np.ndarray, directions: np.ndarray, enabled: Optional[np.ndarray] = None):
+        """Closest near-root hit per ray.  origins/directions: [n,3] float32.  Returns (index[n] int32, t[n] float32)."""
+        if self._scene_id != id(scene):
+            self.upload_scene(scene)
+        o = np.ascontiguousarray(np.asarray(origins, dtype=np.float32).reshape(-1, 3).T)
+        d = np.ascontiguousarray(np.asarray(directions, dtype=np.float32).reshape(-1, 3).T)
+        n = o.shape[1]
+        if d.shape[1] != n:
+            raise ValueError("origins and directions differ in length")
+        en = None
+        if enabled is not None:
+            en = np.ascontiguousarray(np.asarray(enabled).astype(np.uint8))
+            if en.shape != (n,):
+                raise ValueError("enabled mask has the wrong length")
+        idx = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float32)
+        _abi.check(_abi.lib.rtb200_intersect_batch(self._ctx, _ptr(o[0]), _ptr(o[1]), _ptr(o[2]), _ptr(d[0]), _ptr(d[1]), _ptr(d[2]),
+                                                   _ptr(en), n, _ptr(idx), _ptr(t)))
+        return idx, t
+
+    # ---- device-resident entry points (torch owns the memory and the stream) ----------------------------------
+    def trace_device(self, max_bounces: int, samples_per_pixel: int, camera: Camera, accum_ptr: int, stream: int = 0,
+                     sample_range=None, row_range=None) -> None:
+        p = self._params(max_bounces, samples_per_pixel, camera, sample_range, row_range)
+        _abi.check(_abi.lib.rtb200_trace_device(self._ctx, C.byref(camera.abi), C.byref(p), C.c_void_p(accum_ptr), C.c_void_p(stream)))
+
+    def resolve_device(self, accum_ptr: int, n_pixels: int, samples_per_pixel: int, rgb8_ptr: int, stream: int = 0) -> None:
+        _abi.check(_abi.lib.rtb200_resolve_device(self._ctx, C.c_void_p(accum_ptr), int(n_pixels), int(samples_per_pixel),
+                                                  C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
+
+    def intersect_batch_device(self, ptrs, n: int, enabled_ptr: int, idx_ptr: int, t_ptr: int, stream: int = 0) -> None:
+        ox, oy, oz, dx, dy, dz = (C.c_void_p(p) for p in ptrs)
+        _abi.check(_abi.lib.rtb200_intersect_batch_device(self._ctx, ox, oy, oz, dx, dy, dz, C.c_void_p(enabled_ptr) if enabled_ptr else None,
+                                                          int(n), C.c_void_p(idx_ptr), C.c_void_p(t_ptr), C.c_void_p(stream)))
+
+    def read_counters(self) -> Tuple[int, int]:
+        p, s = C.c_uint64(), C.c_uint64()
+        _abi.check(_abi.lib.rtb200_read_counters(self._ctx, C.byref(p), C.byref(s)))
+        return p.value, s.value

@@ -1,0 +1,205 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against oracle<float> on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): intersection — hit/miss and object index exact, t within 1e-5 relative;
+deterministic-mode images — per-channel max abs difference <= 1e-4 before quantisation.  Because the kernels keep the
+reference's operation order and FMA placement, the comparison against oracle<float> is in fact bit-exact, and the
+tests assert that stronger property too (t bit-equal, RGB8 identical, segment counts identical)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+INF = np.float32(np.inf)
+
+
+def _rays(rng, n, scene_arrays, kind="mixed"):
+    spheres = scene_arrays[0]
+    o = rng.uniform(-12, 12, size=(n, 3)).astype(np.float32)
+    o[:, 1] = rng.uniform(0.05, 4.0, size=n).astype(np.float32)
+    tgt = spheres[rng.integers(0, len(spheres), size=n), :3].astype(np.float32)
+    d = tgt - o + rng.normal(0, 0.3, size=(n, 3)).astype(np.float32)
+    if kind == "mixed":
+        scale = rng.uniform(0.1, 2.0, size=(n, 1)).astype(np.float32)   # directions are NOT unit in the reference (F6)
+        d = d * scale
+    rnd = rng.normal(0, 1, size=(n // 4, 3)).astype(np.float32)
+    d[: n // 4] = rnd
+    return o, d
+
+
+def _check_intersect(renderer, oracle, scene, o, d, enabled=None):
+    idx, t = renderer.intersect_batch(scene, o, d, enabled)
+    rays = np.concatenate([o, d], axis=1).astype(np.float64)
+    ridx, rt = oracle.intersect(scene.arrays()[0], rays, enabled, f32=True)
+    assert np.array_equal(idx, ridx), f"{(idx != ridx).sum()} of {len(idx)} indices differ"
+    hit = ridx >= 0
+    assert np.all(np.isinf(t[~hit]))
+    rel = np.abs(t[hit].astype(np.float64) - rt[hit]) / np.abs(rt[hit])
+    assert rel.max(initial=0.0) <= 1e-5
+    assert np.array_equal(t[hit].astype(np.float64), rt[hit])   # bit-exact in practice
+    return idx, t
+
+
+@pytest.mark.parametrize("scene_name,n", [("three_spheres", 20000), ("random_spheres", 20000), ("dielectric_heavy", 5000)])
+def test_intersect_batch_matches_oracle(rtb, renderer, oracle, scene_name, n):
+    scene = getattr(rtb.scenes, scene_name)()
+    o, d = _rays(np.random.default_rng(7), n, scene.arrays())
+    idx, _ = _check_intersect(renderer, oracle, scene, o, d)
+    assert (idx >= 0).mean() > 0.2    # the batch actually exercises hits
+
+
+def test_intersect_batch_ten_k_spheres_tiled(rtb, renderer, oracle):
+    scene = rtb.scenes.ten_k_spheres()
+    o, d = _rays(np.random.default_rng(8), 3000, scene.arrays())
+    _check_intersect(renderer, oracle, scene, o, d)
+
+
+def test_intersect_known_answers(rtb, renderer, oracle):
+    """The hand-derived vectors of SURVEY §8c on the GPU path."""
+    S, M = rtb.Sphere, rtb.Material
+    mats = {"m": M.lambertian((0.5, 0.5, 0.5))}
+    one = rtb.Scene.from_list([S((0.0, 0.0, -1.0), 0.5, "m")], mats)
+    o = np.array([[0, 0, 0], [0, 0, -1], [0, 0, -0.5], [0, 0, -0.5], [0, 0, 0], [0.5, 0, 0], [0, 0, -0.501]], dtype=np.float32)
+    d = np.array([[0, 0, -1], [0, 0, -1], [0, 0, 1], [0, 0, -1], [0, 0, -2], [0, 0, -1], [0, 0, -1]], dtype=np.float32)
+    idx, t = renderer.intersect_batch(one, o, d)
+    assert idx[0] == 0 and t[0] == np.float32(0.5)          # (1) frontal hit
+    assert idx[1] == -1 and np.isinf(t[1])                  # (2) from the centre: near root < 0 -> miss (F4)
+    assert idx[2] == -1 and idx[3] == -1                    # (3) origin on the surface, outward / inward -> miss
+    assert idx[4] == 0 and t[4] == np.float32(0.25)         # (6) non-unit direction: t in units of |d|
+    assert idx[5] == 0 and t[5] == np.float32(1.0)          # (8) tangent ray, disc == 0 -> hit
+    assert idx[6] == -1                                     # origin just inside the surface -> miss
+    two = rtb.Scene.from_list([S((0.0, 0.0, -1.0), 0.5, "m"), S((0.0, 0.0, -1.0), 0.5, "m")], mats)
+    idx, t = renderer.intersect_batch(two, o[:1], d[:1])
+    assert idx[0] == 1                                      # (4) identical spheres: the LAST wins (F5)
+    # (5) t == 0.001 exactly is accepted (inclusive start): sphere whose near root lands on float(0.001)
+    tmin = np.float32(0.001)
+    o5 = np.array([[0, 0, 0]], dtype=np.float32)
+    d5 = np.array([[0, 0, -1]], dtype=np.float32)
+    r5 = 0.5
+    c5 = float(tmin) + r5
+    s5 = rtb.Scene.from_list([S((0.0, 0.0, -c5), r5, "m")], mats)
+    _check_intersect(renderer, oracle, s5, o5, d5)
+    # (7) disabled lanes never hit
+    idx, t = renderer.intersect_batch(one, o[:1].repeat(4, 0), d[:1].repeat(4, 0), np.array([1, 0, 1, 0]))
+    assert list(idx) == [0, -1, 0, -1] and np.isinf(t[1]) and np.isinf(t[3])
+
+
+def test_intersect_empty_and_ragged(rtb, renderer, oracle):
+    scene = rtb.scenes.three_spheres()
+    idx, t = renderer.intersect_batch(scene, np.zeros((0, 3), np.float32), np.zeros((0, 3), np.float32))
+    assert idx.shape == (0,) and t.shape == (0,)
+    for n in (1, 31, 33, 257):
+        o, d = _rays(np.random.default_rng(n), n, scene.arrays())
+        _check_intersect(renderer, oracle, scene, o, d)
+    empty = rtb.Scene.from_list([], {})
+    idx, t = renderer.intersect_batch(empty, np.zeros((5, 3), np.float32), np.ones((5, 3), np.float32))
+    assert np.all(idx == -1) and np.all(np.isinf(t))
+
+
+def _render_both(rtb, renderer, oracle, scene, W, H, spp, depth, seed=1, camera=None, **kw):
+    cam = camera or rtb.Camera.default(W, H)
+    renderer.seed = seed
+    img, lin, stat = renderer.render(depth, spp, scene, cam, want_linear=True, **kw)
+    ref_sum, ref_rgb, ref_seg = oracle.render(scene.arrays(), W, H, cam.vectors(), spp, depth, seed=seed, f32=True,
+                                              sample_range=kw.get("sample_range"), row_range=kw.get("row_range"))
+    return img, lin, stat, ref_sum, ref_rgb, ref_seg
+
+
+@pytest.mark.parametrize("scene_name,W,H,spp", [("three_spheres", 400, 225, 16), ("random_spheres", 192, 108, 8),
+                                                 ("dielectric_heavy", 160, 90, 8)])
+def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp):
+    scene = getattr(rtb.scenes, scene_name)()
+    img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
+    mean = lin[..., :3].astype(np.float64) / spp
+    err = np.abs(mean - ref_sum / spp).max()
+    assert err <= 1e-4, err                              # the north_star tolerance
+    assert stat.segments == ref_seg                      # same paths, same lengths
+    assert stat.paths == W * H * spp
+    assert stat.sphere_tests == ref_seg * len(scene)
+    assert np.array_equal(img, ref_rgb)                  # quantised image identical
+    assert np.all(lin[..., 3] == spp)
+
+
+def test_render_depth_limit_and_seed(rtb, renderer, oracle):
+    scene = rtb.scenes.three_spheres()
+    for depth, seed in ((1, 1), (2, 1), (5, 77), (0, 1)):
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 80, 45, 4, depth, seed=seed)
+        assert np.abs(lin[..., :3] / 4.0 - ref_sum / 4.0).max() <= 1e-4
+        assert stat.segments == ref_seg
+        assert np.array_equal(img, ref_rgb)
+
+
+def test_render_defocus_camera(rtb, renderer, oracle):
+    scene = rtb.scenes.three_spheres()
+    cam = rtb.Camera(120, 68, 10.0, 30.0, (13.0, 2.0, 3.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 0.6)
+    img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 120, 68, 8, 50, camera=cam)
+    assert np.abs(lin[..., :3] / 8.0 - ref_sum / 8.0).max() <= 1e-4
+    assert np.array_equal(img, ref_rgb)
+
+
+def test_render_sharding_is_consistent(rtb, renderer, oracle):
+    """Sample-range and row-range shards reproduce the whole job (what the multi-GPU path relies on)."""
+    scene = rtb.scenes.random_spheres()
+    W, H, spp = 128, 72, 8
+    cam = rtb.Camera.default(W, H)
+    renderer.seed = 3
+    _, whole, st = renderer.render(50, spp, scene, cam, want_linear=True)
+    _, a, sa = renderer.render(50, spp, scene, cam, want_linear=True, sample_range=(0, 3))
+    _, b, sb = renderer.render(50, spp, scene, cam, want_linear=True, sample_range=(3, 8))
+    assert sa.segments + sb.segments == st.segments
+    assert np.abs((a + b)[..., :3] - whole[..., :3]).max() <= 1e-5 * spp
+    assert np.all((a + b)[..., 3] == spp)
+    _, top, _ = renderer.render(50, spp, scene, cam, want_linear=True, row_range=(0, 30))
+    _, bot, _ = renderer.render(50, spp, scene, cam, want_linear=True, row_range=(30, H))
+    assert np.array_equal(top[:30], whole[:30]) and np.array_equal(bot[30:], whole[30:])
+    assert np.all(top[30:] == 0) and np.all(bot[:30] == 0)
+    ref_sum, _, _ = oracle.render(scene.arrays(), W, H, cam.vectors(), spp, 50, seed=3, f32=True, sample_range=(3, 8))
+    assert np.abs(b[..., :3] - ref_sum).max() <= 1e-4 * spp
+
+
+def test_render_is_deterministic(rtb, renderer):
+    scene = rtb.scenes.random_spheres()
+    cam = rtb.Camera.default(160, 90)
+    renderer.seed = 5
+    i1, l1, _ = renderer.render(50, 4, scene, cam, want_linear=True)
+    i2, l2, _ = renderer.render(50, 4, scene, cam, want_linear=True)
+    assert np.array_equal(l1, l2) and np.array_equal(i1, i2)
+    renderer.seed = 6
+    _, l3, _ = renderer.render(50, 4, scene, cam, want_linear=True)
+    assert not np.array_equal(l1, l3)
+
+
+def test_full_size_properties(rtb, renderer):
+    """BASELINE config C2 geometry at full resolution (1920x1080, ~485 spheres), reduced spp: size-independent
+    properties — every path accounted for, sample counts exact, channels within the reference's asserted range
+    (src/color.rs:55-57), sky pixels equal the analytic gradient."""
+    scene = rtb.scenes.random_spheres()
+    W, H, spp = 1920, 1080, 4
+    cam = rtb.Camera.default(W, H)
+    renderer.seed = 1
+    img, lin, stat = renderer.render(50, spp, scene, cam, want_linear=True)
+    assert stat.paths == W * H * spp
+    assert stat.segments >= stat.paths and stat.segments <= stat.paths * 50
+    assert np.all(lin[..., 3] == spp)
+    mean = lin[..., :3] / spp
+    assert np.isfinite(mean).all() and mean.min() >= 0.0 and mean.max() <= 2.0
+    top = mean[:8]            # the first rows look at the sky: blue > green > red, all in the gradient's range
+    assert np.all(top[..., 2] >= top[..., 1]) and np.all(top[..., 1] >= top[..., 0])
+    assert img.shape == (H, W, 3) and img.dtype == np.uint8
+
+
+def test_errors_are_reported_not_fatal(rtb, renderer):
+    scene = rtb.scenes.three_spheres()
+    cam = rtb.Camera.default(16, 9)
+    with pytest.raises(rtb.Rtb200Error):
+        renderer.render(50, 0, scene, cam)                       # spp must be positive
+    with pytest.raises(rtb.Rtb200Error):
+        renderer.render(50, 4, scene, cam, row_range=(0, 99))    # rows out of range
+    with pytest.raises(rtb.Rtb200Error):
+        renderer.render(-1, 4, scene, cam)
+    img, stat = renderer.render(5, 2, scene, cam)                # still usable afterwards
+    assert img.shape == (9, 16, 3)
+
+
+def test_fp32_peak_probe(renderer):
+    tf, ms = renderer.fp32_peak(500)
+    assert 20.0 < tf < 100.0, tf
