@@ -214,6 +214,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
                     s_end = P.sample_begin + (int)((split + 1) * n_samples / P.splits);
                     acc = mk3(0.f, 0.f, 0.f);
                     has_item = true;
+                    if (P.max_bounces <= 0) {               // `for _ in 0..0`: every ray is still enabled => black (:370)
+                        n_paths += (unsigned long long)(s_end - s);
+                        s = s_end;
+                    }
                 } else {
                     exhausted = true;
                 }
