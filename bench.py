@@ -182,7 +182,7 @@ def run_ours(args):
     spp_total = spp_per_gpu * world            # weak scaling: per-GPU work fixed
     scene = getattr(rtb.scenes, gen)()
     cam = rtb.Camera.default(W, H)
-    renderer = rtb.CudaRenderer(device=local_rank, seed=1)
+    renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays)
     tracer = dmod.CudaTracer(renderer, scene)
     sharded = dmod.ShardedRenderer(tracer, mode="samples")
     info = renderer.device_info()
@@ -293,7 +293,7 @@ def run_ours(args):
             "config": {"workload": f"{args.workload}: {gen} {W}x{H}, {spp_per_gpu} spp per GPU ({spp_total} spp total), depth {depth}",
                        "n_spheres": n_spheres, "sharding": "sample-range + NCCL reduce(sum) to rank 0" if world > 1 else "single GPU",
                        "l2": "no reuse across steps: each step re-traces from the camera; inputs are KBs, the framebuffer is written once",
-                       "seed": 1},
+                       "seed": 1, "rays_per_lane": args.rays},
             "sphere_tests_per_s": tests_s, "segments_per_path": segs / max(paths, 1.0),
             "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": peak_tflops, "unit": "TFLOP/s",
                          "frac": achieved_tflops / peak_tflops, "traffic": None,
@@ -321,6 +321,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 1)

@@ -84,6 +84,8 @@ typedef struct rtb200_params {
 } rtb200_params;
 
 #define RTB200_FLAG_NONE 0
+#define RTB200_FLAG_RAYS1 1 /* force the one-ray-per-lane trace kernel  */
+#define RTB200_FLAG_RAYS2 2 /* force the two-rays-per-lane trace kernel */
 
 /* Mirror of RenderStat (src/renderer.rs:11-34) plus the counters the metric needs. */
 typedef struct rtb200_stats {

@@ -1,15 +1,15 @@
 // rt_kernels.cuh — the sm_100a kernels of the render hot path.
 //
-//   sweep_spheres     the closest-hit sweep of one ray against a shared-memory sphere array; the device mirror of
-//                     `for object in &self.objects { object.hit_packed(..) }` (src/ray_tracing.rs:399-401) with
-//                     Sphere::hit_packed (src/objects.rs:249-290) and PackedHitRecords::update (:140-155).
-//                     A warp is the reference's PackedRays<N> with N = 32: one lane per ray, one sphere broadcast
-//                     from shared memory per step (= Simd::splat, src/objects.rs:252-256).
+//   sweep_spheres     the closest-hit sweep of RAYS rays per lane against a shared-memory sphere array; the device
+//                     mirror of `for object in &self.objects { object.hit_packed(..) }` (src/ray_tracing.rs:399-401)
+//                     with Sphere::hit_packed (src/objects.rs:249-290) and PackedHitRecords::update (:140-155).
+//                     A warp is the reference's PackedRays<N> with N = 32*RAYS: one sphere is broadcast from shared
+//                     memory per step (= Simd::splat, src/objects.rs:252-256) and tested against every lane's rays.
 //   k_intersect_batch K1: the sweep alone for a batch of rays (parity + throughput probe).
 //   k_trace_paths     K2: persistent path-tracing kernel — Camera::get_ray + Scene::trace_vectorized* + materials
 //                     + sky + per-pixel accumulation (src/renderer.rs:141-176, src/ray_tracing.rs:77-89, :312-628,
-//                     src/materials.rs:53-147).  Lane = one pixel's sample stream; path regeneration replaces the
-//                     reference's lane compaction (src/ray_tracing.rs:429-483, :561-607).
+//                     src/materials.rs:53-147).  A lane slot = one pixel's sample stream; path regeneration replaces
+//                     the reference's lane compaction (src/ray_tracing.rs:429-483, :561-607).
 //   k_combine         sums the K sample-split partial planes in plane order.
 //   k_resolve         K3: sum/spp + Color::to_u8_array + image assembly (src/renderer.rs:161-163, :376-384;
 //                     src/color.rs:54-64).
@@ -20,41 +20,54 @@
 namespace rtb {
 
 constexpr int SWEEP_BLOCK = 32;          // spheres per candidate-mask word
-constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per lane before a forced flush
+constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per ray before a forced drain
 constexpr float T_MIN = 0.001f;          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
+#define RTB_INF __int_as_float(0x7f800000)
 
 // ---- sphere staging ------------------------------------------------------------------------------------------
-// Device sphere = float4 {cx, cy, cz, r*r}.  The array in shared memory is padded to a multiple of SWEEP_BLOCK with
-// entries whose r*r = -inf: their discriminant is -inf (or NaN), never a hit.
-__device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __restrict__ g_sph, int begin, int count, int padded) {
-    for (int i = threadIdx.x; i < padded; i += blockDim.x) {
-        float4 v = make_float4(0.0f, 0.0f, 0.0f, -__int_as_float(0x7f800000));
-        if (i < count) v = __ldg(&g_sph[begin + i]);
-        s_sph[i] = v;
-    }
+// Device sphere = float4 {cx, cy, cz, r*r}; `count` spheres are copied as they are (no padding: the sweep handles
+// the remainder of the last 32-block with a rolled loop).
+__device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __restrict__ g_sph, int begin, int count) {
+    for (int i = threadIdx.x; i < count; i += blockDim.x) s_sph[i] = __ldg(&g_sph[begin + i]);
+}
+
+// One ray of a lane, as the sweep sees it: origin, direction, a = d.d (src/objects.rs:253) and 1/a (:254).
+struct SweepRay { float ox, oy, oz, dx, dy, dz, a, inv_a; };
+
+__device__ __forceinline__ SweepRay make_sweep_ray(f3 o, f3 d) {
+    SweepRay r;
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.a = plen2_3(d);
+    r.inv_a = __fdiv_rn(1.0f, r.a);
+    return r;
+}
+
+// The discriminant of hit_packed in the reference's operation order (src/objects.rs:252-257):
+// 3 FADD (oc), FMUL + 2 FFMA (half_b), FMUL + 2 FFMA + FADD (c), FMUL + FFMA (disc) = 12 FP32 instructions, 17 FLOP.
+__device__ __forceinline__ float discriminant(const SweepRay& r, float4 s, float& hb) {
+    float ocx = __fsub_rn(r.ox, s.x), ocy = __fsub_rn(r.oy, s.y), ocz = __fsub_rn(r.oz, s.z);       // :252
+    hb = __fmaf_rn(ocz, r.dz, __fmaf_rn(ocy, r.dy, __fmul_rn(ocx, r.dx)));                          // :255
+    float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);       // :256
+    return __fmaf_rn(hb, hb, -__fmul_rn(r.a, cc));                                                  // :257
 }
 
 // Exact per-candidate test: the body of hit_packed's `if discriminant_positive.any()` block for one lane
 // (src/objects.rs:262-288) followed by PackedHitRecords::update (:140-147).
-__device__ __forceinline__ void test_candidate(float4 s, int index, float ox, float oy, float oz, float dx, float dy, float dz,
-                                               float a, float inv_a, float& best_t, int& best_i) {
-    float ocx = __fsub_rn(ox, s.x), ocy = __fsub_rn(oy, s.y), ocz = __fsub_rn(oz, s.z);            // :252
-    float hb = __fmaf_rn(ocz, dz, __fmaf_rn(ocy, dy, __fmul_rn(ocx, dx)));                        // :255
-    float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);     // :256
-    float disc = __fmaf_rn(hb, hb, -__fmul_rn(a, cc));                                            // :257
+__device__ __forceinline__ void test_candidate(const SweepRay& r, float4 s, int index, float& best_t, int& best_i) {
+    float hb;
+    float disc = discriminant(r, s, hb);
     if (disc >= 0.0f) {                                                                            // :259
         float sq = __fsqrt_rn(disc);                                                               // :263
-        float root1 = __fmul_rn(__fsub_rn(-hb, sq), inv_a);                                        // :270
-        bool valid = (root1 >= T_MIN) && (root1 < __int_as_float(0x7f800000));                     // :272-277 (near root only, F4)
+        float root1 = __fmul_rn(__fsub_rn(-hb, sq), r.inv_a);                                      // :270
+        bool valid = (root1 >= T_MIN) && (root1 < RTB_INF);                                        // :272-277 (near root only, F4)
         if (valid && root1 <= best_t) { best_t = root1; best_i = index; }                          // :141 (`<=`: last wins, F5)
     }
 }
 
-// Drains this lane's deferred candidate list in sweep order.  list entry = {sign mask of 32 discriminants, index of
-// the first sphere of that block within the staged array}.
-__device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_base, uint2* list, int list_stride, int& n_list,
-                                                 float ox, float oy, float oz, float dx, float dy, float dz, float a, float inv_a,
-                                                 float& best_t, int& best_i) {
+// Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 discriminants (bit
+// 31 = first sphere of the block, set = not a candidate), index of the block's first sphere in the staged array}.
+__device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_base, const uint2* list, int list_stride, int& n_list,
+                                                 const SweepRay& r, float& best_t, int& best_i) {
     int e = 0;
     uint32_t cand = 0;
     int cbase = 0;
@@ -69,43 +82,81 @@ __device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_
         int j = __clz(cand);
         cand &= ~(0x80000000u >> j);
         int local = cbase + j;
-        test_candidate(s_sph[local], index_base + local, ox, oy, oz, dx, dy, dz, a, inv_a, best_t, best_i);
+        test_candidate(r, s_sph[local], index_base + local, best_t, best_i);
     }
     n_list = 0;
 }
 
-// The sweep over `padded` staged spheres (global indices index_base .. index_base+padded).
+// The sweep of RAYS rays per lane over `count` staged spheres (global indices index_base .. index_base+count).
 //
-// Fast path per sphere (all lanes, no branch): the 12 FP32 operations of the discriminant in the reference's order
-// — 3 FADD (oc), FMUL+2 FFMA (half_b), FMUL+2 FFMA+FADD (c), FMUL+FFMA (disc) = 17 FLOP — plus one funnel shift that
-// appends the discriminant's sign bit to a 32-sphere mask.  A set sign bit means disc < 0 (or disc = -0.0, which only
-// arises when half_b = +-0 and then root1 = +-0 < 0.001: not a hit either), so candidates are the clear bits.
-// Slow path (deferred, lane-parallel): masks with a clear bit are pushed to a per-lane list in shared memory and
-// re-tested exactly (sqrt, root, range, `<=`) after the sweep, in sweep order.
-__device__ __forceinline__ void sweep_spheres(const float4* s_sph, int padded, int index_base, uint2* list, int list_stride,
-                                              float ox, float oy, float oz, float dx, float dy, float dz, float a, float inv_a,
-                                              float& best_t, int& best_i) {
-    int n_list = 0;
-    for (int blk = 0; blk < padded; blk += SWEEP_BLOCK) {
-        uint32_t mask = 0;
+// Fast path per (sphere, ray), all lanes, no branch: the 12 FP32 operations of the discriminant plus ONE funnel shift
+// that appends the discriminant's sign bit to a 32-sphere mask word; one LDS.128 per sphere serves all RAYS rays of the
+// lane.  A set sign bit means disc < 0 (or disc = -0.0, which needs half_b = +-0 and then root1 = +-0 < 0.001: not a hit
+// either), so candidates are the clear bits.
+// Slow path (deferred, lane-parallel): mask words with a clear bit are pushed to a per-ray list in shared memory and
+// re-tested exactly (sqrt, root, range, `<=`) after the sweep, in sweep order — so the result is that of the
+// reference's sequential `update` over the object list.
+// list layout: entry e of ray r of this thread at list[(r * LIST_CAP + e) * list_stride].
+template <int RAYS>
+__device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, int index_base, uint2* list, int list_stride,
+                                              const SweepRay (&ray)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+    int n_list[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) n_list[r] = 0;
+    const int full = count & ~(SWEEP_BLOCK - 1);
+    for (int blk = 0; blk < full; blk += SWEEP_BLOCK) {
+        uint32_t mask[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = 0;
 #pragma unroll
         for (int j = 0; j < SWEEP_BLOCK; j++) {
             float4 s = s_sph[blk + j];                                                            // LDS.128 broadcast = Simd::splat
-            float ocx = __fsub_rn(ox, s.x), ocy = __fsub_rn(oy, s.y), ocz = __fsub_rn(oz, s.z);
-            float hb = __fmaf_rn(ocz, dz, __fmaf_rn(ocy, dy, __fmul_rn(ocx, dx)));
-            float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);
-            float disc = __fmaf_rn(hb, hb, -__fmul_rn(a, cc));
-            mask = __funnelshift_l(__float_as_uint(disc), mask, 1);                               // mask = (mask << 1) | sign(disc)
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                float hb;
+                float disc = discriminant(ray[r], s, hb);
+                mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);                     // (mask << 1) | sign(disc)
+            }
         }
-        if (mask != 0xffffffffu) {
-            list[n_list * list_stride] = make_uint2(mask, (uint32_t)blk);
-            n_list++;
-            if (n_list == LIST_CAP)
-                drain_candidates(s_sph, index_base, list, list_stride, n_list, ox, oy, oz, dx, dy, dz, a, inv_a, best_t, best_i);
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            if (mask[r] != 0xffffffffu) {
+                list[(r * LIST_CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
+                n_list[r]++;
+                if (n_list[r] == LIST_CAP)
+                    drain_candidates(s_sph, index_base, list + r * LIST_CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+            }
         }
     }
-    if (n_list > 0)
-        drain_candidates(s_sph, index_base, list, list_stride, n_list, ox, oy, oz, dx, dy, dz, a, inv_a, best_t, best_i);
+    const int rem = count - full;                     // 0..31 spheres left: rolled loop, same arithmetic
+    if (rem > 0) {
+        uint32_t mask[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = 0;
+#pragma unroll 2
+        for (int j = 0; j < rem; j++) {
+            float4 s = s_sph[full + j];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                float hb;
+                float disc = discriminant(ray[r], s, hb);
+                mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);
+            }
+        }
+        const uint32_t fill = 0xffffffffu >> rem;     // the 32-rem unused low positions read as "not a candidate"
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            uint32_t m = (mask[r] << (32 - rem)) | fill;
+            if (m != 0xffffffffu) {
+                list[(r * LIST_CAP + n_list[r]) * list_stride] = make_uint2(m, (uint32_t)full);
+                n_list[r]++;
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < RAYS; r++)
+        if (n_list[r] > 0)
+            drain_candidates(s_sph, index_base, list + r * LIST_CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
 }
 
 // ---- K1 ----------------------------------------------------------------------------------------------------------
@@ -122,24 +173,22 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     uint2* list = reinterpret_cast<uint2*>(smem4 + tile) + threadIdx.x;
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     bool live = i < n_rays;
-    float rox = 0.f, roy = 0.f, roz = 0.f, rdx = 0.f, rdy = 0.f, rdz = 0.f;
-    if (live) { rox = ox[i]; roy = oy[i]; roz = oz[i]; rdx = dx[i]; rdy = dy[i]; rdz = dz[i]; }
-    float a = plen2_3(mk3(rdx, rdy, rdz));                     // src/objects.rs:253
-    float inv_a = __fdiv_rn(1.0f, a);                          // :254
-    float best_t = __int_as_float(0x7f800000);                 // PackedHitRecords::default, src/objects.rs:121-134
-    int best_i = -1;
+    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
+    if (live) { o = mk3(ox[i], oy[i], oz[i]); d = mk3(dx[i], dy[i], dz[i]); }
+    SweepRay ray[1] = {make_sweep_ray(o, d)};
+    float best_t[1] = {RTB_INF};                               // PackedHitRecords::default, src/objects.rs:121-134
+    int best_i[1] = {-1};
     for (int begin = 0; begin < n_spheres; begin += tile) {
         int count = min(tile, n_spheres - begin);
-        int padded = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK * SWEEP_BLOCK;
         __syncthreads();
-        stage_spheres(s_sph, g_sph, begin, count, padded);
+        stage_spheres(s_sph, g_sph, begin, count);
         __syncthreads();
-        sweep_spheres(s_sph, padded, begin, list, blockDim.x, rox, roy, roz, rdx, rdy, rdz, a, inv_a, best_t, best_i);
+        sweep_spheres<1>(s_sph, count, begin, list, blockDim.x, ray, best_t, best_i);
     }
     if (live) {
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
-        hit_index[i] = en ? best_i : -1;
-        hit_t[i] = (en && best_i >= 0) ? best_t : __int_as_float(0x7f800000);
+        hit_index[i] = en ? best_i[0] : -1;
+        hit_t[i] = (en && best_i[0] >= 0) ? best_t[0] : RTB_INF;
     }
 }
 
@@ -150,7 +199,6 @@ struct TraceParams {
     const float4* mat;            // per sphere {albedo rgb, param}
     const int* mat_kind;          // per sphere kind | hollow<<8
     int n_spheres;
-    int padded;                   // n_spheres rounded up to SWEEP_BLOCK
     int max_bounces;
     uint32_t seed_lo, seed_hi;
     int sample_begin, sample_end; // global sample indices traced by this launch
@@ -161,15 +209,29 @@ struct TraceParams {
     unsigned long long* counters; // [0] paths, [1] segments
 };
 
-// Persistent kernel.  Work item = (pixel of the row range, sample split).  A lane owns one item at a time and runs its
-// samples one after another (path regeneration); the per-pixel sum is a private register sum in sample order, so the
-// image is deterministic and needs no atomics.  dynamic smem: padded float4 + LIST_CAP * blockDim uint2.
-template <int THREADS, int MIN_BLOCKS>
+// One path slot of a lane.  A slot owns one work item (a pixel and a contiguous range of its samples) at a time and
+// runs the samples one after another; the per-pixel sum `acc` is a private sum in sample order, so the image is
+// deterministic and needs no atomics.
+struct PathSlot {
+    f3 o, d;                      // current ray (direction NOT normalised after scatter, src/ray.rs:13-18)
+    f3 thr, acc;                  // path throughput (`color`, src/ray_tracing.rs:319) and the pixel's running sum
+    uint32_t pixel_id;            // row * W + col: Philox counter word 0
+    uint32_t out_off;             // float4 index into P.out
+    int s, s_end, n_s;            // next sample, end of the item's sample range, its length
+    int bounce;
+    bool has_item, has_path;
+};
+
+// Persistent kernel: grid = SMs x resident CTAs.  Every loop trip makes ONE closest-hit sweep for all slots of the
+// warp, then per slot: terminate (sky / depth limit) or keep the hit; finished items are written out and new ones
+// claimed with one atomic per warp; then ONE Philox block per slot feeds either the next camera ray or the scatter.
+// dynamic smem: n_spheres float4 + RAYS * LIST_CAP * THREADS uint2.
+template <int THREADS, int MIN_BLOCKS, int RAYS>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const TraceParams P) {
     extern __shared__ float4 smem4[];
     float4* s_sph = smem4;
-    uint2* list = reinterpret_cast<uint2*>(smem4 + P.padded) + threadIdx.x;
-    stage_spheres(s_sph, P.spheres, 0, P.n_spheres, P.padded);
+    uint2* list = reinterpret_cast<uint2*>(smem4 + ((P.n_spheres + 1) & ~1)) + threadIdx.x;
+    stage_spheres(s_sph, P.spheres, 0, P.n_spheres);
     __syncthreads();
 
     const int W = P.cam.width;
@@ -178,106 +240,140 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     const int n_samples = P.sample_end - P.sample_begin;
     const unsigned lane = threadIdx.x & 31u;
 
-    // lane state
-    bool has_item = false, has_path = false, exhausted = false;
-    unsigned long long item = 0;
-    int col = 0, row = 0, s = 0, s_first = 0, s_end = 0, bounce = 0;
-    uint32_t pixel_id = 0;
-    f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
-    f3 thr = mk3(1.f, 1.f, 1.f), acc = mk3(0.f, 0.f, 0.f);
-    unsigned long long n_segments = 0, n_paths = 0;
+    PathSlot slot[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) {
+        slot[r].o = mk3(0.f, 0.f, 0.f); slot[r].d = mk3(0.f, 0.f, 1.f);
+        slot[r].thr = mk3(1.f, 1.f, 1.f); slot[r].acc = mk3(0.f, 0.f, 0.f);
+        slot[r].pixel_id = 0; slot[r].out_off = 0; slot[r].s = 0; slot[r].s_end = 0; slot[r].n_s = 0; slot[r].bounce = 0;
+        slot[r].has_item = false; slot[r].has_path = false;
+    }
+    bool exhausted = false;
+    unsigned n_segments = 0, n_paths = 0;          // per-lane counts (a lane traces far fewer than 2^32 segments)
+    float best_t[RAYS];
+    int best_i[RAYS];
+    bool swept = false;
 
     for (;;) {
-        // ---- regeneration: finished items are written out, new items claimed with one atomic per warp ----
-        if (has_item && !has_path && s >= s_end) {
-            unsigned long long split = item / n_pix, pix = item % n_pix;
-            size_t off = (P.splits == 1) ? ((size_t)P.row_begin * W + pix) : (size_t)(split * n_pix + pix);
-            P.out[off] = make_float4(acc.x, acc.y, acc.z, (float)(s_end - s_first));
-            has_item = false;
-        }
-        bool need = !has_item && !exhausted;
-        unsigned need_mask = __ballot_sync(0xffffffffu, need);
-        if (need_mask) {
-            unsigned long long base = 0;
-            int leader = __ffs(need_mask) - 1;
-            if ((int)lane == leader) base = atomicAdd(P.work_counter, (unsigned long long)__popc(need_mask));
-            base = __shfl_sync(0xffffffffu, base, leader);
-            if (need) {
-                item = base + __popc(need_mask & ((1u << lane) - 1u));
-                if (item < n_items) {
-                    unsigned long long split = item / n_pix, pix = item % n_pix;
-                    row = P.row_begin + (int)(pix / W);
-                    col = (int)(pix % W);
-                    pixel_id = (uint32_t)row * (uint32_t)W + (uint32_t)col;
-                    s_first = P.sample_begin + (int)(split * n_samples / P.splits);
-                    s = s_first;
-                    s_end = P.sample_begin + (int)((split + 1) * n_samples / P.splits);
-                    acc = mk3(0.f, 0.f, 0.f);
-                    has_item = true;
-                    if (P.max_bounces <= 0) {               // `for _ in 0..0`: every ray is still enabled => black (:370)
-                        n_paths += (unsigned long long)(s_end - s);
-                        s = s_end;
+        // ---- 1. after a sweep: terminate paths that escaped or reached the depth limit ----
+        if (swept) {
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                PathSlot& q = slot[r];
+                if (q.has_path) {
+                    n_segments++;
+                    if (best_i[r] < 0) {                       // hit the sky (src/ray_tracing.rs:353-357, :365-369)
+                        f3 sk = sky(q.d);
+                        q.acc = add3(q.acc, mk3(__fmul_rn(q.thr.x, sk.x), __fmul_rn(q.thr.y, sk.y), __fmul_rn(q.thr.z, sk.z)));
+                        q.has_path = false;
+                        q.s++;
+                    } else if (q.bounce + 1 >= P.max_bounces) { // still enabled after the last bounce => black (:370)
+                        q.has_path = false;
+                        q.s++;
                     }
-                } else {
-                    exhausted = true;
                 }
             }
         }
-        if (has_item && !has_path && s < s_end) {
-            uint4 rnd = philox4x32_10(pixel_id, (uint32_t)s, RTB_DIM_CAMERA, 0u, P.seed_lo, P.seed_hi);
-            camera_get_ray(P.cam, col, row, rnd, o, d);
-            thr = mk3(1.f, 1.f, 1.f);
-            bounce = 0;
-            has_path = true;
-            n_paths++;
+        // ---- 2. finished items are written out; new items are claimed with one atomic per warp ----
+        unsigned need_mask[RAYS];
+        int n_need = 0;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            PathSlot& q = slot[r];
+            if (q.has_item && !q.has_path && q.s >= q.s_end) {
+                P.out[q.out_off] = make_float4(q.acc.x, q.acc.y, q.acc.z, (float)q.n_s);
+                q.has_item = false;
+            }
+            need_mask[r] = __ballot_sync(0xffffffffu, !q.has_item && !exhausted);
+            n_need += __popc(need_mask[r]);
         }
-        if (!__any_sync(0xffffffffu, has_path)) {
-            if (__all_sync(0xffffffffu, exhausted && !has_item)) break;
-            continue;   // items with an empty sample range
-        }
-
-        // ---- closest-hit sweep (all lanes; lanes without a path sweep a dummy ray and ignore the result) ----
-        float a = plen2_3(d);                                   // src/objects.rs:253
-        float inv_a = __fdiv_rn(1.0f, a);                       // :254
-        float best_t = __int_as_float(0x7f800000);
-        int best_i = -1;
-        sweep_spheres(s_sph, P.padded, 0, list, THREADS, o.x, o.y, o.z, d.x, d.y, d.z, a, inv_a, best_t, best_i);
-
-        // ---- shade ----
-        if (has_path) {
-            n_segments++;
-            if (best_i < 0) {                                   // hit the sky (src/ray_tracing.rs:353-357, :365-369)
-                f3 sk = sky(d);
-                acc = add3(acc, mk3(__fmul_rn(thr.x, sk.x), __fmul_rn(thr.y, sk.y), __fmul_rn(thr.z, sk.z)));
-                has_path = false;
-                s++;
-            } else {
-                float4 sp = s_sph[best_i];
-                HitRec rec = finalize_hit(o, d, best_t, mk3(sp.x, sp.y, sp.z));
-                uint4 rnd = philox4x32_10(pixel_id, (uint32_t)s, 1u + (uint32_t)bounce, 0u, P.seed_lo, P.seed_hi);
-                f3 att, nd;
-                scatter(__ldg(&P.mat_kind[best_i]), __ldg(&P.mat[best_i]), d, rec, rnd, att, nd);
-                thr = mk3(__fmul_rn(thr.x, att.x), __fmul_rn(thr.y, att.y), __fmul_rn(thr.z, att.z));
-                o = rec.p;
-                d = nd;
-                bounce++;
-                if (bounce >= P.max_bounces) {                  // still enabled at the depth limit => black (:370)
-                    has_path = false;
-                    s++;
+        if (n_need) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(P.work_counter, (unsigned long long)n_need);
+            base = __shfl_sync(0xffffffffu, base, 0);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                PathSlot& q = slot[r];
+                if (!q.has_item && !exhausted) {
+                    unsigned long long item = base + __popc(need_mask[r] & ((1u << lane) - 1u));
+                    if (item < n_items) {
+                        unsigned long long split = item / n_pix, pix = item - split * n_pix;
+                        q.pixel_id = (uint32_t)((unsigned long long)P.row_begin * W + pix);
+                        q.out_off = (P.splits == 1) ? q.pixel_id : (uint32_t)item;
+                        q.s = P.sample_begin + (int)(split * n_samples / P.splits);
+                        q.s_end = P.sample_begin + (int)((split + 1) * n_samples / P.splits);
+                        q.n_s = q.s_end - q.s;
+                        q.acc = mk3(0.f, 0.f, 0.f);
+                        q.has_item = true;
+                        if (P.max_bounces <= 0) {              // `for _ in 0..0`: every ray stays enabled => black (:370)
+                            n_paths += (unsigned)q.n_s;
+                            q.s = q.s_end;
+                        }
+                    } else {
+                        exhausted = true;
+                    }
                 }
+                base += __popc(need_mask[r]);
             }
         }
+        // ---- 3. one Philox block per slot: the next camera sample, or this bounce's scatter ----
+        bool any_path = false;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            PathSlot& q = slot[r];
+            const bool regen = q.has_item && !q.has_path && q.s < q.s_end;
+            if (regen || q.has_path) {
+                uint4 rnd = philox4x32_10(q.pixel_id, (uint32_t)q.s, regen ? RTB_DIM_CAMERA : 1u + (uint32_t)q.bounce, 0u, P.seed_lo, P.seed_hi);
+                if (regen) {                                   // Camera::get_ray, src/ray_tracing.rs:77-89
+                    int row = (int)(q.pixel_id / (uint32_t)W), col = (int)(q.pixel_id - (uint32_t)row * (uint32_t)W);
+                    camera_get_ray(P.cam, col, row, rnd, q.o, q.d);
+                    q.thr = mk3(1.f, 1.f, 1.f);
+                    q.bounce = 0;
+                    q.has_path = true;
+                    n_paths++;
+                } else {                                       // finalize + Material::get_hit_result (src/ray_tracing.rs:335-346)
+                    float4 sp = s_sph[best_i[r]];
+                    HitRec rec = finalize_hit(q.o, q.d, best_t[r], mk3(sp.x, sp.y, sp.z));
+                    f3 att, nd;
+                    scatter(__ldg(&P.mat_kind[best_i[r]]), __ldg(&P.mat[best_i[r]]), q.d, rec, rnd, att, nd);
+                    q.thr = mk3(__fmul_rn(q.thr.x, att.x), __fmul_rn(q.thr.y, att.y), __fmul_rn(q.thr.z, att.z));
+                    q.o = rec.p;
+                    q.d = nd;
+                    q.bounce++;
+                }
+            }
+            any_path = any_path || q.has_path;
+        }
+        if (!__any_sync(0xffffffffu, any_path)) {
+            bool idle = exhausted;
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) idle = idle && !slot[r].has_item;
+            if (__all_sync(0xffffffffu, idle)) break;
+            swept = false;
+            continue;                                          // items with an empty sample range: write out, claim again
+        }
+        // ---- 4. the closest-hit sweep (all lanes; a slot without a path sweeps its stale ray and the result is ignored)
+        SweepRay ray[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            ray[r] = make_sweep_ray(slot[r].o, slot[r].d);
+            best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
+            best_i[r] = -1;
+        }
+        sweep_spheres<RAYS>(s_sph, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
+        swept = true;
     }
 
     // ---- counters: one atomic pair per warp ----
+    unsigned long long seg64 = n_segments, path64 = n_paths;
 #pragma unroll
     for (int sh = 16; sh > 0; sh >>= 1) {
-        n_segments += __shfl_xor_sync(0xffffffffu, n_segments, sh);
-        n_paths += __shfl_xor_sync(0xffffffffu, n_paths, sh);
+        seg64 += __shfl_xor_sync(0xffffffffu, seg64, sh);
+        path64 += __shfl_xor_sync(0xffffffffu, path64, sh);
     }
     if (lane == 0) {
-        atomicAdd(&P.counters[0], n_paths);
-        atomicAdd(&P.counters[1], n_segments);
+        atomicAdd(&P.counters[0], path64);
+        atomicAdd(&P.counters[1], seg64);
     }
 }
 

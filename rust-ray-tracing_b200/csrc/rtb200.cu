@@ -27,10 +27,12 @@ int fail(int code, const std::string& msg) {
             return fail(RTB200_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));                   \
     } while (0)
 
-constexpr int SMALL_THREADS = 256, SMALL_BLOCKS = 4;   // scenes whose staging fits four CTAs per SM
-constexpr int LARGE_THREADS = 1024, LARGE_BLOCKS = 1;  // one CTA per SM, up to ~11k spheres resident in shared memory
+constexpr int SMALL_THREADS = 256;    // scenes whose staging leaves room for several CTAs per SM
+constexpr int LARGE_THREADS = 1024;   // one CTA per SM, up to ~11k spheres resident in shared memory
 
-size_t trace_smem_bytes(int padded, int threads) { return (size_t)padded * sizeof(float4) + (size_t)rtb::LIST_CAP * threads * sizeof(uint2); }
+size_t trace_smem_bytes(int n_spheres, int threads, int rays) {
+    return (size_t)((n_spheres + 1) & ~1) * sizeof(float4) + (size_t)rays * rtb::LIST_CAP * threads * sizeof(uint2);
+}
 
 }  // namespace
 
@@ -54,6 +56,7 @@ struct rtb200_ctx {
     int64_t launches = 0;
     size_t max_optin_smem = 0;
     bool attrs_set = false;
+    int default_rays = 1;
 };
 
 namespace {
@@ -115,7 +118,6 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     P.cam = device_camera(*cam);
     P.spheres = ctx->d_spheres; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
     P.n_spheres = ctx->n_spheres;
-    P.padded = (ctx->n_spheres + rtb::SWEEP_BLOCK - 1) / rtb::SWEEP_BLOCK * rtb::SWEEP_BLOCK;
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
     P.sample_begin = p->sample_begin; P.sample_end = p->sample_end;
@@ -135,19 +137,30 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     } else {
         P.out = accum;
     }
+    if ((unsigned long long)n_pix * (unsigned long long)P.splits >= (1ull << 32))
+        return fail(RTB200_ERR_INVALID, "too many work items for one launch");
+    // Kernel variants: <threads, resident CTAs per SM, rays per lane>.
+    auto k_s1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1>;
+    auto k_s2 = rtb::k_trace_paths<SMALL_THREADS, 3, 2>;
+    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1>;
     if (!ctx->attrs_set) {
-        CU_TRY(cudaFuncSetAttribute(rtb::k_trace_paths<SMALL_THREADS, SMALL_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(rtb::k_trace_paths<LARGE_THREADS, LARGE_BLOCKS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_s1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_s2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
     }
     const int sms = ctx->prop.multiProcessorCount;
-    size_t smem_small = trace_smem_bytes(P.padded, SMALL_THREADS);
-    size_t smem_large = trace_smem_bytes(P.padded, LARGE_THREADS);
-    size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
-    if ((smem_small + 1024) * SMALL_BLOCKS <= per_sm) {
-        rtb::k_trace_paths<SMALL_THREADS, SMALL_BLOCKS><<<sms * SMALL_BLOCKS, SMALL_THREADS, smem_small, st>>>(P);
-    } else if (smem_large <= ctx->max_optin_smem) {
-        rtb::k_trace_paths<LARGE_THREADS, LARGE_BLOCKS><<<sms * LARGE_BLOCKS, LARGE_THREADS, smem_large, st>>>(P);
+    const size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
+    const size_t smem_s1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1);
+    const size_t smem_s2 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 2);
+    const size_t smem_l1 = trace_smem_bytes(P.n_spheres, LARGE_THREADS, 1);
+    int variant = (p->flags & RTB200_FLAG_RAYS2) ? 2 : (p->flags & RTB200_FLAG_RAYS1) ? 1 : ctx->default_rays;
+    if (variant == 2 && (smem_s2 + 1024) * 3 <= per_sm) {
+        k_s2<<<sms * 3, SMALL_THREADS, smem_s2, st>>>(P);
+    } else if ((smem_s1 + 1024) * 4 <= per_sm) {
+        k_s1<<<sms * 4, SMALL_THREADS, smem_s1, st>>>(P);
+    } else if (smem_l1 <= ctx->max_optin_smem) {
+        k_l1<<<sms, LARGE_THREADS, smem_l1, st>>>(P);
     } else {
         return fail(RTB200_ERR_INVALID, "scene too large for shared-memory staging (" + std::to_string(ctx->n_spheres) + " spheres)");
     }
@@ -177,7 +190,7 @@ int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const fl
     if (n <= 0) return RTB200_OK;
     const int threads = 256;
     int padded_all = (ctx->n_spheres + rtb::SWEEP_BLOCK - 1) / rtb::SWEEP_BLOCK * rtb::SWEEP_BLOCK;
-    int tile = padded_all < 2048 ? padded_all : 2048;
+    int tile = padded_all < 2048 ? padded_all : 2048;    // multiple of SWEEP_BLOCK: only the last tile has a remainder
     if (tile < rtb::SWEEP_BLOCK) tile = rtb::SWEEP_BLOCK;
     size_t smem = (size_t)tile * sizeof(float4) + (size_t)rtb::LIST_CAP * threads * sizeof(uint2);
     static bool attr = false;

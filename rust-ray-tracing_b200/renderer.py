@@ -48,7 +48,9 @@ class CudaRenderer(Renderer):
     equivalents are the CUDA device and the Philox seed of the sample stream.
     """
 
-    def __init__(self, device: int = 0, seed: int = 1):
+    def __init__(self, device: int = 0, seed: int = 1, rays_per_lane: int = 0):
+        """rays_per_lane: 0 = the library's default trace kernel, 1 / 2 = force that variant (RTB200_FLAG_RAYS1/2)."""
+        self.rays_per_lane = int(rays_per_lane)
         self._ctx = C.c_void_p()
         _abi.check(_abi.lib.rtb200_create(int(device), C.byref(self._ctx)))
         self.device = int(device)
@@ -93,7 +95,8 @@ class CudaRenderer(Renderer):
     def _params(self, max_bounces, spp, camera, sample_range, row_range) -> _abi.Params:
         s0, s1 = sample_range if sample_range is not None else (0, spp)
         r0, r1 = row_range if row_range is not None else (0, camera.image_height())
-        return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), 0, 0)
+        flags = {0: 0, 1: 1, 2: 2}[self.rays_per_lane]
+        return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), flags, 0)
 
     # ---- Renderer::render -------------------------------------------------------------------------------------
     def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera, *, want_linear: bool = False,

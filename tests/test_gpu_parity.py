@@ -104,10 +104,12 @@ def _render_both(rtb, renderer, oracle, scene, W, H, spp, depth, seed=1, camera=
     return img, lin, stat, ref_sum, ref_rgb, ref_seg
 
 
+@pytest.mark.parametrize("rays", [1, 2])
 @pytest.mark.parametrize("scene_name,W,H,spp", [("three_spheres", 400, 225, 16), ("random_spheres", 192, 108, 8),
                                                  ("dielectric_heavy", 160, 90, 8)])
-def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp):
+def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp, rays):
     scene = getattr(rtb.scenes, scene_name)()
+    renderer.rays_per_lane = rays
     img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
     mean = lin[..., :3].astype(np.float64) / spp
     err = np.abs(mean - ref_sum / spp).max()
@@ -117,15 +119,19 @@ def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp):
     assert stat.sphere_tests == ref_seg * len(scene)
     assert np.array_equal(img, ref_rgb)                  # quantised image identical
     assert np.all(lin[..., 3] == spp)
+    renderer.rays_per_lane = 0
 
 
-def test_render_depth_limit_and_seed(rtb, renderer, oracle):
+@pytest.mark.parametrize("rays", [1, 2])
+def test_render_depth_limit_and_seed(rtb, renderer, oracle, rays):
     scene = rtb.scenes.three_spheres()
+    renderer.rays_per_lane = rays
     for depth, seed in ((1, 1), (2, 1), (5, 77), (0, 1)):
         img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 80, 45, 4, depth, seed=seed)
         assert np.abs(lin[..., :3] / 4.0 - ref_sum / 4.0).max() <= 1e-4
         assert stat.segments == ref_seg
         assert np.array_equal(img, ref_rgb)
+    renderer.rays_per_lane = 0
 
 
 def test_render_defocus_camera(rtb, renderer, oracle):
