@@ -97,41 +97,37 @@ class ClockSampler:
 
 
 def cpu_reference_run(workload: str, steps: int, warmup: int, budget_s: float = 12.0):
-    """Times the CPU port of the reference's path (oracle/, all host threads) on a bounded sample of the workload:
-    same scene and camera at reduced resolution and spp, sized for roughly `budget_s` seconds per step."""
+    """Times the CPU port of the reference's LIVE path (oracle/cpu_ref.cpp: TileRenderer + render_vectorized2 +
+    trace_vectorized2 + hit_packed, 4 x f64 AVX2 lanes, 128x128 tiles, all host threads) on a bounded sample of the
+    workload: same scene, camera and spp at a quarter of the resolution in each dimension (1/16 of the pixels), further
+    reduced in spp if a calibration pass says one step would exceed `budget_s` seconds."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as oracle
     from importlib import import_module
-    rtb_scene = import_module(PKG + ".scene")
     rtb_scenes = import_module(PKG + ".scenes")
     gen, W, H, spp, depth = WORKLOADS[workload]
     scene = getattr(rtb_scenes, gen)()
     arrays = scene.arrays()
     cores = os.cpu_count() or 1
+    sw, sh = max(16, W // 4), max(9, H // 4)
     # camera through the oracle's own Camera::new (no GPU library involved on this arm)
-    sw, sh = max(16, W // 8), max(9, H // 8)
     cam = oracle.camera_new(sw, sh, 10.0, 30.0, (16.0, 2.0, 18.5), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 0.0)
-    # calibrate: 1 spp pass
-    t0 = time.perf_counter()
-    oracle.render(arrays, sw, sh, cam, 1, depth, seed=1, f32=False, want_rgb8=False, threads=cores)
-    t1 = time.perf_counter() - t0
-    s_spp = max(1, min(spp, int(budget_s / max(t1, 1e-6))))
-    times, segs = [], 0
+    _, t4, _, _ = oracle.cpuref_render(arrays, sw, sh, cam, 4, depth, threads=cores, want_rgb8=False)   # calibrate: 4 spp
+    s_spp = max(4, min(spp, int(budget_s / max(t4 / 4.0, 1e-6)) // 4 * 4))
+    times, segs, tests = [], 0, 0
     for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        _, _, segs = oracle.render(arrays, sw, sh, cam, s_spp, depth, seed=1, f32=False, want_rgb8=True, threads=cores)
-        dt = time.perf_counter() - t0
+        _, sec, tests, segs = oracle.cpuref_render(arrays, sw, sh, cam, s_spp, depth, threads=cores, want_rgb8=True)
         if i >= warmup:
-            times.append(dt)
+            times.append(sec)
     paths = sw * sh * s_spp
     sec = sum(times) / len(times)
     return {
         "mpaths_s": paths / sec * 1e-6,
-        "tests_s": segs * len(scene) / sec,
+        "tests_s": tests / sec,
         "ms_per_step": sec * 1e3,
         "cores": cores,
-        "sample": f"{gen} {sw}x{sh} (same camera), {s_spp} spp, depth {depth}: {paths} paths/step, scalar f64 per-path port "
-                  f"of trace_vectorized* + hit_packed on {cores} threads",
+        "sample": f"{gen} {sw}x{sh} (same camera, 1/16 of the pixels), {s_spp} spp, depth {depth}: {paths} paths/step; C++ port of "
+                  f"TileRenderer + trace_vectorized2 + hit_packed (4 x f64 AVX2 lanes, 128x128 tiles) on {cores} threads",
         "n_spheres": len(scene),
     }
 

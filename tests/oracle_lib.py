@@ -138,3 +138,29 @@ def render(scene_arrays, width, height, cam18, spp, depth, seed=1, sample_range=
                        int(r0), int(r1), int(threads), int(f32), _d(out_sum),
                        out_rgb.ctypes.data_as(C.POINTER(C.c_uint8)) if want_rgb8 else None, C.byref(seg))
     return out_sum, out_rgb, int(seg.value)
+
+
+# ---- CPU baseline port of the reference's live renderer (oracle/cpu_ref.cpp) ---------------------------------
+CPUREF = os.path.join(ORACLE_DIR, "libcpuref.so")
+_cpuref = C.CDLL(CPUREF)
+_cpuref.cpuref_render.restype = C.c_double
+
+
+def cpuref_render(scene_arrays, width, height, cam18, spp, depth, threads=0, block_size=128, seed=1, row_range=None, want_rgb8=True):
+    """TileRenderer + render_vectorized2 + trace_vectorized2 (4 x f64 AVX2 lanes, own PRNG).
+    Returns (rgb8[H,W,3], seconds, lane_tests, segments)."""
+    spheres, mat_index, kind, hollow, albedo, param = scene_arrays
+    r0, r1 = row_range if row_range is not None else (0, height)
+    sp = np.ascontiguousarray(spheres, dtype=np.float64)
+    mi = np.ascontiguousarray(mat_index, dtype=np.int32)
+    kd = np.ascontiguousarray(kind, dtype=np.int32)
+    hl = np.ascontiguousarray(hollow, dtype=np.int32)
+    al = np.ascontiguousarray(albedo, dtype=np.float64)
+    pr = np.ascontiguousarray(param, dtype=np.float64)
+    cam = np.ascontiguousarray(cam18, dtype=np.float64)
+    rgb = np.zeros((height, width, 3), dtype=np.uint8)
+    tests, seg = C.c_uint64(0), C.c_uint64(0)
+    sec = _cpuref.cpuref_render(_d(sp), _i(mi), int(sp.shape[0]), _i(kd), _i(hl), _d(al), _d(pr), int(kd.shape[0]), int(width), int(height),
+                                _d(cam), int(spp), int(depth), int(threads), int(block_size), C.c_uint64(seed), int(r0), int(r1),
+                                rgb.ctypes.data_as(C.POINTER(C.c_uint8)) if want_rgb8 else None, C.byref(tests), C.byref(seg))
+    return rgb, float(sec), int(tests.value), int(seg.value)
