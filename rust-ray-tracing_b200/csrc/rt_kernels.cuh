@@ -20,7 +20,8 @@
 namespace rtb {
 
 constexpr int SWEEP_BLOCK = 32;          // spheres per candidate-mask word
-constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per ray before a forced drain
+constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per ray before a forced drain (general case)
+constexpr int LIST_CAP_SMALL = 16;       // scenes of <= 512 spheres: one entry per 32-block always fits, no overflow check
 constexpr float T_MIN = 0.001f;          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
 #define RTB_INF __int_as_float(0x7f800000)
 
@@ -96,8 +97,9 @@ __device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_
 // Slow path (deferred, lane-parallel): mask words with a clear bit are pushed to a per-ray list in shared memory and
 // re-tested exactly (sqrt, root, range, `<=`) after the sweep, in sweep order — so the result is that of the
 // reference's sequential `update` over the object list.
-// list layout: entry e of ray r of this thread at list[(r * LIST_CAP + e) * list_stride].
-template <int RAYS>
+// list layout: entry e of ray r of this thread at list[(r * CAP + e) * list_stride].  CAP >= number of 32-blocks
+// (CHECKED = false) removes the overflow test from the per-block path.
+template <int RAYS, int CAP, bool CHECKED>
 __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, int index_base, uint2* list, int list_stride,
                                               const SweepRay (&ray)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
     int n_list[RAYS];
@@ -108,23 +110,27 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
         uint32_t mask[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) mask[r] = 0;
+        constexpr int UNROLL = SWEEP_BLOCK / RAYS;      // keep the unrolled body at ~450 instructions (instruction cache)
+#pragma unroll 1
+        for (int sub = 0; sub < SWEEP_BLOCK; sub += UNROLL) {
 #pragma unroll
-        for (int j = 0; j < SWEEP_BLOCK; j++) {
-            float4 s = s_sph[blk + j];                                                            // LDS.128 broadcast = Simd::splat
+            for (int j = 0; j < UNROLL; j++) {
+                float4 s = s_sph[blk + sub + j];                                                  // LDS.128 broadcast = Simd::splat
 #pragma unroll
-            for (int r = 0; r < RAYS; r++) {
-                float hb;
-                float disc = discriminant(ray[r], s, hb);
-                mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);                     // (mask << 1) | sign(disc)
+                for (int r = 0; r < RAYS; r++) {
+                    float hb;
+                    float disc = discriminant(ray[r], s, hb);
+                    mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);                 // (mask << 1) | sign(disc)
+                }
             }
         }
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             if (mask[r] != 0xffffffffu) {
-                list[(r * LIST_CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
+                list[(r * CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
                 n_list[r]++;
-                if (n_list[r] == LIST_CAP)
-                    drain_candidates(s_sph, index_base, list + r * LIST_CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+                if (CHECKED && n_list[r] == CAP)
+                    drain_candidates(s_sph, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
             }
         }
     }
@@ -148,7 +154,7 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
         for (int r = 0; r < RAYS; r++) {
             uint32_t m = (mask[r] << (32 - rem)) | fill;
             if (m != 0xffffffffu) {
-                list[(r * LIST_CAP + n_list[r]) * list_stride] = make_uint2(m, (uint32_t)full);
+                list[(r * CAP + n_list[r]) * list_stride] = make_uint2(m, (uint32_t)full);
                 n_list[r]++;
             }
         }
@@ -156,7 +162,7 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
 #pragma unroll
     for (int r = 0; r < RAYS; r++)
         if (n_list[r] > 0)
-            drain_candidates(s_sph, index_base, list + r * LIST_CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+            drain_candidates(s_sph, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
 }
 
 // ---- K1 ----------------------------------------------------------------------------------------------------------
@@ -183,7 +189,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
         __syncthreads();
         stage_spheres(s_sph, g_sph, begin, count);
         __syncthreads();
-        sweep_spheres<1>(s_sph, count, begin, list, blockDim.x, ray, best_t, best_i);
+        sweep_spheres<1, LIST_CAP, true>(s_sph, count, begin, list, blockDim.x, ray, best_t, best_i);
     }
     if (live) {
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
@@ -203,8 +209,9 @@ struct TraceParams {
     uint32_t seed_lo, seed_hi;
     int sample_begin, sample_end; // global sample indices traced by this launch
     int row_begin, row_end;
-    int splits;                   // K: sample range is cut into K contiguous sub-ranges, one work item each
-    float4* out;                  // splits == 1: accum image (W*H float4); else partial planes [K][rows*W]
+    int splits_log2;              // K = 1 << splits_log2: the sample range is cut into K contiguous sub-ranges, one work item each
+    uint32_t width_magic;         // floor(2^32 / W) + 1 (0 when W == 1): row = pixel / W by multiply-high
+    float4* out;                  // K == 1: accum image (W*H float4); else partial planes [K][rows*W]
     unsigned long long* work_counter;
     unsigned long long* counters; // [0] paths, [1] segments
 };
@@ -225,8 +232,8 @@ struct PathSlot {
 // Persistent kernel: grid = SMs x resident CTAs.  Every loop trip makes ONE closest-hit sweep for all slots of the
 // warp, then per slot: terminate (sky / depth limit) or keep the hit; finished items are written out and new ones
 // claimed with one atomic per warp; then ONE Philox block per slot feeds either the next camera ray or the scatter.
-// dynamic smem: n_spheres float4 + RAYS * LIST_CAP * THREADS uint2.
-template <int THREADS, int MIN_BLOCKS, int RAYS>
+// dynamic smem: n_spheres float4 + RAYS * CAP * THREADS uint2.  CAP = LIST_CAP_SMALL needs n_spheres <= 32 * CAP.
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const TraceParams P) {
     extern __shared__ float4 smem4[];
     float4* s_sph = smem4;
@@ -235,9 +242,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     __syncthreads();
 
     const int W = P.cam.width;
-    const unsigned long long n_pix = (unsigned long long)(P.row_end - P.row_begin) * (unsigned long long)W;
-    const unsigned long long n_items = n_pix * (unsigned long long)P.splits;
-    const int n_samples = P.sample_end - P.sample_begin;
+    const uint32_t n_pix = (uint32_t)(P.row_end - P.row_begin) * (uint32_t)W;
+    const uint32_t n_items = n_pix << P.splits_log2;          // host guarantees < 2^32
+    const uint32_t n_samples = (uint32_t)(P.sample_end - P.sample_begin);
+    const uint32_t first_pixel = (uint32_t)P.row_begin * (uint32_t)W;
     const unsigned lane = threadIdx.x & 31u;
 
     PathSlot slot[RAYS];
@@ -288,20 +296,23 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
             n_need += __popc(need_mask[r]);
         }
         if (n_need) {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(P.work_counter, (unsigned long long)n_need);
-            base = __shfl_sync(0xffffffffu, base, 0);
+            unsigned long long base64 = 0;
+            if (lane == 0) base64 = atomicAdd(P.work_counter, (unsigned long long)n_need);
+            base64 = __shfl_sync(0xffffffffu, base64, 0);
+            // items beyond n_items (< 2^32) saturate: the queue head only ever overshoots by the number of lanes
+            uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
                 PathSlot& q = slot[r];
                 if (!q.has_item && !exhausted) {
-                    unsigned long long item = base + __popc(need_mask[r] & ((1u << lane) - 1u));
-                    if (item < n_items) {
-                        unsigned long long split = item / n_pix, pix = item - split * n_pix;
-                        q.pixel_id = (uint32_t)((unsigned long long)P.row_begin * W + pix);
-                        q.out_off = (P.splits == 1) ? q.pixel_id : (uint32_t)item;
-                        q.s = P.sample_begin + (int)(split * n_samples / P.splits);
-                        q.s_end = P.sample_begin + (int)((split + 1) * n_samples / P.splits);
+                    uint32_t rank = __popc(need_mask[r] & ((1u << lane) - 1u));
+                    uint32_t item = base + rank;
+                    if (item >= base && item < n_items) {      // item = pixel * K + split: a warp works on neighbouring pixels
+                        uint32_t split = item & ((1u << P.splits_log2) - 1u), pix = item >> P.splits_log2;
+                        q.pixel_id = first_pixel + pix;
+                        q.out_off = (P.splits_log2 == 0) ? q.pixel_id : split * n_pix + pix;
+                        q.s = P.sample_begin + (int)(((unsigned long long)split * n_samples) >> P.splits_log2);
+                        q.s_end = P.sample_begin + (int)(((unsigned long long)(split + 1) * n_samples) >> P.splits_log2);
                         q.n_s = q.s_end - q.s;
                         q.acc = mk3(0.f, 0.f, 0.f);
                         q.has_item = true;
@@ -313,7 +324,8 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
                         exhausted = true;
                     }
                 }
-                base += __popc(need_mask[r]);
+                uint32_t adv = __popc(need_mask[r]);
+                base = (base + adv < base) ? 0xffffffffu : base + adv;
             }
         }
         // ---- 3. one Philox block per slot: the next camera sample, or this bounce's scatter ----
@@ -325,7 +337,9 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
             if (regen || q.has_path) {
                 uint4 rnd = philox4x32_10(q.pixel_id, (uint32_t)q.s, regen ? RTB_DIM_CAMERA : 1u + (uint32_t)q.bounce, 0u, P.seed_lo, P.seed_hi);
                 if (regen) {                                   // Camera::get_ray, src/ray_tracing.rs:77-89
-                    int row = (int)(q.pixel_id / (uint32_t)W), col = (int)(q.pixel_id - (uint32_t)row * (uint32_t)W);
+                    uint32_t rowu = P.width_magic ? __umulhi(q.pixel_id, P.width_magic) : q.pixel_id;   // pixel / W
+                    if (rowu * (uint32_t)W > q.pixel_id) rowu--;                                       // estimate is q or q+1
+                    int row = (int)rowu, col = (int)(q.pixel_id - rowu * (uint32_t)W);
                     camera_get_ray(P.cam, col, row, rnd, q.o, q.d);
                     q.thr = mk3(1.f, 1.f, 1.f);
                     q.bounce = 0;
@@ -360,7 +374,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
             best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
             best_i[r] = -1;
         }
-        sweep_spheres<RAYS>(s_sph, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
+        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(s_sph, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
         swept = true;
     }
 

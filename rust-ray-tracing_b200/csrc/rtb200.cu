@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -30,8 +31,8 @@ int fail(int code, const std::string& msg) {
 constexpr int SMALL_THREADS = 256;    // scenes whose staging leaves room for several CTAs per SM
 constexpr int LARGE_THREADS = 1024;   // one CTA per SM, up to ~11k spheres resident in shared memory
 
-size_t trace_smem_bytes(int n_spheres, int threads, int rays) {
-    return (size_t)((n_spheres + 1) & ~1) * sizeof(float4) + (size_t)rays * rtb::LIST_CAP * threads * sizeof(uint2);
+size_t trace_smem_bytes(int n_spheres, int threads, int rays, int cap) {
+    return (size_t)((n_spheres + 1) & ~1) * sizeof(float4) + (size_t)rays * cap * threads * sizeof(uint2);
 }
 
 }  // namespace
@@ -95,17 +96,16 @@ int validate_params(const rtb200_ctx* ctx, const rtb200_camera* cam, const rtb20
     return RTB200_OK;
 }
 
-// Chooses the number of sample splits K so that the persistent grid has many more work items than lanes
-// (tail balance) while each item keeps several samples (register-resident sum).
-int choose_splits(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
+// Chooses log2 of the number of sample splits K (a power of two) so that the persistent grid has many more work items
+// than lanes (tail balance) while each item keeps at least 8 samples (register-resident sum).  RTB200_SPLITS_LOG2
+// overrides (tuning aid).
+int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
+    if (const char* e = std::getenv("RTB200_SPLITS_LOG2")) { int v = std::atoi(e); if (v >= 0 && v <= 6) return v; }
     long long lanes = (long long)ctx->prop.multiProcessorCount * 1024;
-    long long want_items = lanes * 24;
-    long long k = (want_items + n_pix - 1) / (n_pix > 0 ? n_pix : 1);
-    long long kmax = n_samples / 4;
-    if (k > kmax) k = kmax;
-    if (k < 1) k = 1;
-    if (k > 64) k = 64;
-    return (int)k;
+    long long want_items = lanes * 64;
+    int lg = 0;
+    while (lg < 6 && (n_pix << lg) < want_items && (n_samples >> (lg + 1)) >= 8) lg++;
+    return lg;
 }
 
 int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p, float4* accum, cudaStream_t st) {
@@ -122,11 +122,13 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
     P.sample_begin = p->sample_begin; P.sample_end = p->sample_end;
     P.row_begin = p->row_begin; P.row_end = p->row_end;
-    P.splits = choose_splits(ctx, n_pix, n_samples);
+    P.splits_log2 = choose_splits_log2(ctx, n_pix, n_samples);
+    const int splits = 1 << P.splits_log2;
+    P.width_magic = W > 1 ? (uint32_t)((1ull << 32) / (unsigned long long)W) + 1u : 0u;
     P.work_counter = ctx->d_counters + 2;
     P.counters = ctx->d_counters;
-    if (P.splits > 1) {
-        size_t want = (size_t)P.splits * (size_t)n_pix;
+    if (splits > 1) {
+        size_t want = (size_t)splits * (size_t)n_pix;
         if (ctx->partial_elems < want) {
             if (ctx->d_partial) cudaFree(ctx->d_partial);
             ctx->d_partial = nullptr; ctx->partial_elems = 0;
@@ -137,28 +139,35 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     } else {
         P.out = accum;
     }
-    if ((unsigned long long)n_pix * (unsigned long long)P.splits >= (1ull << 32))
+    if ((unsigned long long)n_pix * (unsigned long long)splits >= (1ull << 32) - 65536)
         return fail(RTB200_ERR_INVALID, "too many work items for one launch");
-    // Kernel variants: <threads, resident CTAs per SM, rays per lane>.
-    auto k_s1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1>;
-    auto k_s2 = rtb::k_trace_paths<SMALL_THREADS, 3, 2>;
-    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1>;
+    // Kernel variants: <threads, resident CTAs per SM, rays per lane, candidate-list capacity>.
+    constexpr int CS = rtb::LIST_CAP_SMALL, CG = rtb::LIST_CAP;
+    auto k_s1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CS>;     // <= 512 spheres: unchecked lists
+    auto k_s2 = rtb::k_trace_paths<SMALL_THREADS, 3, 2, CS>;
+    auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;     // up to ~2 000 spheres with four CTAs per SM
+    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;     // up to ~11 000 spheres, one CTA per SM
     if (!ctx->attrs_set) {
         CU_TRY(cudaFuncSetAttribute(k_s1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_s2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
     }
     const int sms = ctx->prop.multiProcessorCount;
     const size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
-    const size_t smem_s1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1);
-    const size_t smem_s2 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 2);
-    const size_t smem_l1 = trace_smem_bytes(P.n_spheres, LARGE_THREADS, 1);
+    const size_t smem_s1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1, CS);
+    const size_t smem_s2 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 2, CS);
+    const size_t smem_m1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1, CG);
+    const size_t smem_l1 = trace_smem_bytes(P.n_spheres, LARGE_THREADS, 1, CG);
+    const bool small = P.n_spheres <= 32 * CS;
     int variant = (p->flags & RTB200_FLAG_RAYS2) ? 2 : (p->flags & RTB200_FLAG_RAYS1) ? 1 : ctx->default_rays;
-    if (variant == 2 && (smem_s2 + 1024) * 3 <= per_sm) {
+    if (small && variant == 2 && (smem_s2 + 1024) * 3 <= per_sm) {
         k_s2<<<sms * 3, SMALL_THREADS, smem_s2, st>>>(P);
-    } else if ((smem_s1 + 1024) * 4 <= per_sm) {
+    } else if (small && (smem_s1 + 1024) * 4 <= per_sm) {
         k_s1<<<sms * 4, SMALL_THREADS, smem_s1, st>>>(P);
+    } else if ((smem_m1 + 1024) * 4 <= per_sm) {
+        k_m1<<<sms * 4, SMALL_THREADS, smem_m1, st>>>(P);
     } else if (smem_l1 <= ctx->max_optin_smem) {
         k_l1<<<sms, LARGE_THREADS, smem_l1, st>>>(P);
     } else {
@@ -166,9 +175,9 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     }
     CU_TRY(cudaGetLastError());
     ctx->launches++;
-    if (P.splits > 1) {
+    if (splits > 1) {
         int blocks = (int)((n_pix + 255) / 256);
-        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, P.splits, n_pix, accum + (size_t)p->row_begin * W);
+        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, splits, n_pix, accum + (size_t)p->row_begin * W);
         CU_TRY(cudaGetLastError());
         ctx->launches++;
     }
