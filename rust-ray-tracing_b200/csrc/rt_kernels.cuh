@@ -16,6 +16,7 @@
 //   k_fp32_peak       K0: dependent-free FFMA chains, the measured FP32 roofline for this path.
 #pragma once
 #include "rt_device.cuh"
+#include "rt_filter.h"
 
 namespace rtb {
 
@@ -26,49 +27,54 @@ constexpr float T_MIN = 0.001f;          // 0.001..f64::INFINITY (src/ray_tracin
 #define RTB_INF __int_as_float(0x7f800000)
 
 // ---- sphere staging ------------------------------------------------------------------------------------------
-// Device sphere = float4 {cx, cy, cz, r*r}; `count` spheres are copied as they are (no padding: the sweep handles
+// Two device arrays per scene, both in list order: the EXACT spheres float4 {cx, cy, cz, r*r} (global memory, read
+// only by the candidate re-test and by shading) and the FILTER spheres float4 {cx, cy, cz, k} (rt_filter.h), which
+// are what the sweep stages in shared memory.  `count` spheres are copied as they are (no padding: the sweep handles
 // the remainder of the last 32-block with a rolled loop).
-__device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __restrict__ g_sph, int begin, int count) {
-    for (int i = threadIdx.x; i < count; i += blockDim.x) s_sph[i] = __ldg(&g_sph[begin + i]);
+__device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __restrict__ g_flt, int begin, int count) {
+    for (int i = threadIdx.x; i < count; i += blockDim.x) s_sph[i] = __ldg(&g_flt[begin + i]);
 }
 
-// One ray of a lane, as the sweep sees it: origin, direction, a = d.d (src/objects.rs:253) and 1/a (:254).
-struct SweepRay { float ox, oy, oz, dx, dy, dz, a, inv_a; };
+// One ray of a lane, as the sweep sees it: origin, direction, and the ray's half of the candidate filter.
+// a = d.d (src/objects.rs:253) and 1/a (:254) are recomputed where the exact test needs them (once per drain).
+struct SweepRay { float ox, oy, oz, dx, dy, dz; FilterRay f; };
 
 __device__ __forceinline__ SweepRay make_sweep_ray(f3 o, f3 d) {
     SweepRay r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
-    r.a = plen2_3(d);
-    r.inv_a = __fdiv_rn(1.0f, r.a);
+    r.f = make_filter_ray(o.x, o.y, o.z, d.x, d.y, d.z, plen2_3(d));
     return r;
 }
 
 // The discriminant of hit_packed in the reference's operation order (src/objects.rs:252-257):
 // 3 FADD (oc), FMUL + 2 FFMA (half_b), FMUL + 2 FFMA + FADD (c), FMUL + FFMA (disc) = 12 FP32 instructions, 17 FLOP.
-__device__ __forceinline__ float discriminant(const SweepRay& r, float4 s, float& hb) {
+__device__ __forceinline__ float discriminant(const SweepRay& r, float a, float4 s, float& hb) {
     float ocx = __fsub_rn(r.ox, s.x), ocy = __fsub_rn(r.oy, s.y), ocz = __fsub_rn(r.oz, s.z);       // :252
     hb = __fmaf_rn(ocz, r.dz, __fmaf_rn(ocy, r.dy, __fmul_rn(ocx, r.dx)));                          // :255
     float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);       // :256
-    return __fmaf_rn(hb, hb, -__fmul_rn(r.a, cc));                                                  // :257
+    return __fmaf_rn(hb, hb, -__fmul_rn(a, cc));                                                    // :257
 }
 
 // Exact per-candidate test: the body of hit_packed's `if discriminant_positive.any()` block for one lane
 // (src/objects.rs:262-288) followed by PackedHitRecords::update (:140-147).
-__device__ __forceinline__ void test_candidate(const SweepRay& r, float4 s, int index, float& best_t, int& best_i) {
+__device__ __forceinline__ void test_candidate(const SweepRay& r, float a, float inv_a, float4 s, int index, float& best_t, int& best_i) {
     float hb;
-    float disc = discriminant(r, s, hb);
+    float disc = discriminant(r, a, s, hb);
     if (disc >= 0.0f) {                                                                            // :259
         float sq = __fsqrt_rn(disc);                                                               // :263
-        float root1 = __fmul_rn(__fsub_rn(-hb, sq), r.inv_a);                                      // :270
+        float root1 = __fmul_rn(__fsub_rn(-hb, sq), inv_a);                                        // :270
         bool valid = (root1 >= T_MIN) && (root1 < RTB_INF);                                        // :272-277 (near root only, F4)
         if (valid && root1 <= best_t) { best_t = root1; best_i = index; }                          // :141 (`<=`: last wins, F5)
     }
 }
 
-// Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 discriminants (bit
+// Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 filter values (bit
 // 31 = first sphere of the block, set = not a candidate), index of the block's first sphere in the staged array}.
-__device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_base, const uint2* list, int list_stride, int& n_list,
+// g_exact = the exact spheres of the staged range (global memory, L1-resident).
+__device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_exact, int index_base, const uint2* list, int list_stride, int& n_list,
                                                  const SweepRay& r, float& best_t, int& best_i) {
+    const float a = plen2_3(mk3(r.dx, r.dy, r.dz));                                                // :253
+    const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
     int e = 0;
     uint32_t cand = 0;
     int cbase = 0;
@@ -83,7 +89,7 @@ __device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_
         int j = __clz(cand);
         cand &= ~(0x80000000u >> j);
         int local = cbase + j;
-        test_candidate(r, s_sph[local], index_base + local, best_t, best_i);
+        test_candidate(r, a, inv_a, __ldg(&g_exact[local]), index_base + local, best_t, best_i);
     }
     n_list = 0;
 }
@@ -100,7 +106,8 @@ __device__ __forceinline__ void drain_candidates(const float4* s_sph, int index_
 // list layout: entry e of ray r of this thread at list[(r * CAP + e) * list_stride].  CAP >= number of 32-blocks
 // (CHECKED = false) removes the overflow test from the per-block path.
 template <int RAYS, int CAP, bool CHECKED>
-__device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, int index_base, uint2* list, int list_stride,
+__device__ __forceinline__ void sweep_spheres(const float4* s_sph, const float4* __restrict__ g_exact, int count, int index_base,
+                                              uint2* list, int list_stride,
                                               const SweepRay (&ray)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
     int n_list[RAYS];
 #pragma unroll
@@ -118,9 +125,8 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
                 float4 s = s_sph[blk + sub + j];                                                  // LDS.128 broadcast = Simd::splat
 #pragma unroll
                 for (int r = 0; r < RAYS; r++) {
-                    float hb;
-                    float disc = discriminant(ray[r], s, hb);
-                    mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);                 // (mask << 1) | sign(disc)
+                    float q = filter_value(ray[r].f, s.x, s.y, s.z, s.w);                         // 8 FP32 instructions
+                    mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);                    // (mask << 1) | sign(q)
                 }
             }
         }
@@ -130,7 +136,7 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
                 list[(r * CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
                 n_list[r]++;
                 if (CHECKED && n_list[r] == CAP)
-                    drain_candidates(s_sph, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+                    drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
             }
         }
     }
@@ -144,9 +150,8 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
             float4 s = s_sph[full + j];
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
-                float hb;
-                float disc = discriminant(ray[r], s, hb);
-                mask[r] = __funnelshift_l(__float_as_uint(disc), mask[r], 1);
+                float q = filter_value(ray[r].f, s.x, s.y, s.z, s.w);
+                mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);
             }
         }
         const uint32_t fill = 0xffffffffu >> rem;     // the 32-rem unused low positions read as "not a candidate"
@@ -162,13 +167,13 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, int count, in
 #pragma unroll
     for (int r = 0; r < RAYS; r++)
         if (n_list[r] > 0)
-            drain_candidates(s_sph, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+            drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
 }
 
 // ---- K1 ----------------------------------------------------------------------------------------------------------
 // One thread per ray; spheres streamed through shared memory in tiles of `tile` (multiple of SWEEP_BLOCK).
 // dynamic smem: tile float4 + LIST_CAP * blockDim uint2.
-__global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restrict__ g_sph, int n_spheres, int tile,
+__global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restrict__ g_sph, const float4* __restrict__ g_flt, int n_spheres, int tile,
                                                          const float* __restrict__ ox, const float* __restrict__ oy,
                                                          const float* __restrict__ oz, const float* __restrict__ dx,
                                                          const float* __restrict__ dy, const float* __restrict__ dz,
@@ -187,9 +192,9 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     for (int begin = 0; begin < n_spheres; begin += tile) {
         int count = min(tile, n_spheres - begin);
         __syncthreads();
-        stage_spheres(s_sph, g_sph, begin, count);
+        stage_spheres(s_sph, g_flt, begin, count);
         __syncthreads();
-        sweep_spheres<1, LIST_CAP, true>(s_sph, count, begin, list, blockDim.x, ray, best_t, best_i);
+        sweep_spheres<1, LIST_CAP, true>(s_sph, g_sph + begin, count, begin, list, blockDim.x, ray, best_t, best_i);
     }
     if (live) {
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
@@ -201,7 +206,8 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
 // ---- K2 ----------------------------------------------------------------------------------------------------------
 struct TraceParams {
     DeviceCamera cam;
-    const float4* spheres;        // {cx,cy,cz,r*r}
+    const float4* spheres;        // exact: {cx,cy,cz,r*r}
+    const float4* filter;         // candidate filter: {cx,cy,cz,k} (rt_filter.h)
     const float4* mat;            // per sphere {albedo rgb, param}
     const int* mat_kind;          // per sphere kind | hollow<<8
     int n_spheres;
@@ -238,7 +244,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     extern __shared__ float4 smem4[];
     float4* s_sph = smem4;
     uint2* list = reinterpret_cast<uint2*>(smem4 + ((P.n_spheres + 1) & ~1)) + threadIdx.x;
-    stage_spheres(s_sph, P.spheres, 0, P.n_spheres);
+    stage_spheres(s_sph, P.filter, 0, P.n_spheres);
     __syncthreads();
 
     const int W = P.cam.width;
@@ -374,7 +380,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
             best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
             best_i[r] = -1;
         }
-        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(s_sph, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
+        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(s_sph, P.spheres, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
         swept = true;
     }
 

@@ -42,6 +42,7 @@ struct rtb200_ctx {
     cudaDeviceProp prop{};
     // scene
     float4* d_spheres = nullptr;
+    float4* d_filter = nullptr;
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
     int n_spheres = 0;
@@ -116,7 +117,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const int n_samples = p->sample_end - p->sample_begin;
     rtb::TraceParams P;
     P.cam = device_camera(*cam);
-    P.spheres = ctx->d_spheres; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
+    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
     P.n_spheres = ctx->n_spheres;
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
@@ -209,7 +210,7 @@ int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const fl
     }
     long long blocks = (n + threads - 1) / threads;
     if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
-    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t);
+    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->d_filter, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t);
     CU_TRY(cudaGetLastError());
     ctx->launches++;
     return RTB200_OK;
@@ -252,7 +253,7 @@ int rtb200_create(int32_t device, rtb200_ctx** out) {
 void rtb200_destroy(rtb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_spheres); cudaFree(c->d_mat); cudaFree(c->d_mat_kind); cudaFree(c->d_counters);
+    cudaFree(c->d_spheres); cudaFree(c->d_filter); cudaFree(c->d_mat); cudaFree(c->d_mat_kind); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     delete c;
@@ -304,7 +305,7 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     if (scene->n_spheres < 0 || scene->n_materials < 0) return fail(RTB200_ERR_INVALID, "negative count");
     if (scene->n_spheres > 0 && (!scene->spheres || !scene->materials)) return fail(RTB200_ERR_INVALID, "null scene arrays");
     const int n = scene->n_spheres;
-    std::vector<float4> sph((size_t)(n > 0 ? n : 1)), mat((size_t)(n > 0 ? n : 1));
+    std::vector<float4> sph((size_t)(n > 0 ? n : 1)), flt((size_t)(n > 0 ? n : 1)), mat((size_t)(n > 0 ? n : 1));
     std::vector<int> kind((size_t)(n > 0 ? n : 1));
     for (int i = 0; i < n; i++) {
         const rtb200_sphere& s = scene->spheres[i];
@@ -313,6 +314,10 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         const rtb200_material& m = scene->materials[s.material];
         float r = (float)s.radius;
         sph[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], r * r);   // radius.powi(2), src/objects.rs:256
+        // The f32 path squares coordinates: keep them far from overflow (the reference is f64 and has no such limit).
+        if (!(std::fabs(sph[i].x) <= 1e15f && std::fabs(sph[i].y) <= 1e15f && std::fabs(sph[i].z) <= 1e15f && std::fabs(r) <= 1e15f))
+            return fail(RTB200_ERR_INVALID, "sphere " + std::to_string(i) + ": centre/radius not finite or beyond 1e15 (f32 device path)");
+        flt[i] = make_float4(sph[i].x, sph[i].y, sph[i].z, rtb::filter_sphere_k(sph[i].x, sph[i].y, sph[i].z, sph[i].w));
         double param = m.param;
         if (m.kind == RTB200_METAL) param = (param < 1.0) ? param : 1.0;                           // Metal::new, src/materials.rs:79-88
         else if (m.kind != RTB200_LAMBERTIAN && m.kind != RTB200_DIELECTRIC)
@@ -321,13 +326,15 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         kind[i] = m.kind | ((m.kind == RTB200_DIELECTRIC && m.hollow) ? RTB_HOLLOW_BIT : 0);
     }
     CU_TRY(cudaSetDevice(ctx->device));
-    cudaFree(ctx->d_spheres); cudaFree(ctx->d_mat); cudaFree(ctx->d_mat_kind);
-    ctx->d_spheres = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
+    cudaFree(ctx->d_spheres); cudaFree(ctx->d_filter); cudaFree(ctx->d_mat); cudaFree(ctx->d_mat_kind);
+    ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
     size_t cnt = (size_t)(n > 0 ? n : 1);
     CU_TRY(cudaMalloc(&ctx->d_spheres, cnt * sizeof(float4)));
+    CU_TRY(cudaMalloc(&ctx->d_filter, cnt * sizeof(float4)));
     CU_TRY(cudaMalloc(&ctx->d_mat, cnt * sizeof(float4)));
     CU_TRY(cudaMalloc(&ctx->d_mat_kind, cnt * sizeof(int)));
     CU_TRY(cudaMemcpy(ctx->d_spheres, sph.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(ctx->d_filter, flt.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
     CU_TRY(cudaMemcpy(ctx->d_mat, mat.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
     CU_TRY(cudaMemcpy(ctx->d_mat_kind, kind.data(), cnt * sizeof(int), cudaMemcpyHostToDevice));
     ctx->n_spheres = n;
