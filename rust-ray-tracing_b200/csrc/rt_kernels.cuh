@@ -23,6 +23,7 @@ namespace rtb {
 constexpr int SWEEP_BLOCK = 32;          // spheres per candidate-mask word
 constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per ray before a forced drain (general case)
 constexpr int LIST_CAP_SMALL = 16;       // scenes of <= 512 spheres: one entry per 32-block always fits, no overflow check
+constexpr int LIST_CAP_V = 8;            // parameter-space variant (two rays per lane, path state in shared memory)
 constexpr float T_MIN = 0.001f;          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
 #define RTB_INF __int_as_float(0x7f800000)
 
@@ -35,20 +36,20 @@ __device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __res
     for (int i = threadIdx.x; i < count; i += blockDim.x) s_sph[i] = __ldg(&g_flt[begin + i]);
 }
 
-// One ray of a lane, as the sweep sees it: origin, direction, and the ray's half of the candidate filter.
-// a = d.d (src/objects.rs:253) and 1/a (:254) are recomputed where the exact test needs them (once per drain).
-struct SweepRay { float ox, oy, oz, dx, dy, dz; FilterRay f; };
+// One ray as the exact candidate test needs it (origin, direction as stored: never normalised, src/ray.rs:13-18).
+struct ExactRay { float ox, oy, oz, dx, dy, dz; };
 
-__device__ __forceinline__ SweepRay make_sweep_ray(f3 o, f3 d) {
-    SweepRay r;
+__device__ __forceinline__ ExactRay make_exact_ray(f3 o, f3 d) {
+    ExactRay r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
-    r.f = make_filter_ray(o.x, o.y, o.z, d.x, d.y, d.z, plen2_3(d));
     return r;
 }
+// The ray's half of the candidate filter; a = d.d as the sweep computes it (src/objects.rs:253).
+__device__ __forceinline__ FilterRay make_filter(f3 o, f3 d) { return make_filter_ray(o.x, o.y, o.z, d.x, d.y, d.z, plen2_3(d)); }
 
 // The discriminant of hit_packed in the reference's operation order (src/objects.rs:252-257):
 // 3 FADD (oc), FMUL + 2 FFMA (half_b), FMUL + 2 FFMA + FADD (c), FMUL + FFMA (disc) = 12 FP32 instructions, 17 FLOP.
-__device__ __forceinline__ float discriminant(const SweepRay& r, float a, float4 s, float& hb) {
+__device__ __forceinline__ float discriminant(const ExactRay& r, float a, float4 s, float& hb) {
     float ocx = __fsub_rn(r.ox, s.x), ocy = __fsub_rn(r.oy, s.y), ocz = __fsub_rn(r.oz, s.z);       // :252
     hb = __fmaf_rn(ocz, r.dz, __fmaf_rn(ocy, r.dy, __fmul_rn(ocx, r.dx)));                          // :255
     float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);       // :256
@@ -57,7 +58,7 @@ __device__ __forceinline__ float discriminant(const SweepRay& r, float a, float4
 
 // Exact per-candidate test: the body of hit_packed's `if discriminant_positive.any()` block for one lane
 // (src/objects.rs:262-288) followed by PackedHitRecords::update (:140-147).
-__device__ __forceinline__ void test_candidate(const SweepRay& r, float a, float inv_a, float4 s, int index, float& best_t, int& best_i) {
+__device__ __forceinline__ void test_candidate(const ExactRay& r, float a, float inv_a, float4 s, int index, float& best_t, int& best_i) {
     float hb;
     float disc = discriminant(r, a, s, hb);
     if (disc >= 0.0f) {                                                                            // :259
@@ -68,11 +69,28 @@ __device__ __forceinline__ void test_candidate(const SweepRay& r, float a, float
     }
 }
 
+// Where the sweep reads its warp-uniform sphere operand from.
+//   SmemSpheres : the staged shared-memory array (LDS.128 -> 4 registers; a chain FFMA then reads 3 registers, which
+//                 costs two register-file cycles unless the operand-reuse cache hits: ~12.5 cycles per warp-test).
+//   ParamSpheres: the kernel's parameter space (constant bank 0; LDCU.64 x2 -> 4 UNIFORM registers; a chain FFMA then
+//                 reads 2 registers + 1 uniform register: one cycle.  ~11 cycles per warp-test with two rays per lane;
+//                 tools/filter_probe.cu, profiles/r1_filter_probe.txt).  Up to N spheres (32 KB of parameters).
+struct SmemSpheres {
+    const float4* p;
+    __device__ __forceinline__ float4 at(int i) const { return p[i]; }
+};
+
+// Where the drain reads a lane's rays from: registers (resident kernel) or the lane's path state in shared memory.
+struct RegisterRays {
+    const ExactRay* ray;
+    __device__ __forceinline__ ExactRay load(int r) const { return ray[r]; }
+};
+
 // Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 filter values (bit
 // 31 = first sphere of the block, set = not a candidate), index of the block's first sphere in the staged array}.
 // g_exact = the exact spheres of the staged range (global memory, L1-resident).
 __device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_exact, int index_base, const uint2* list, int list_stride, int& n_list,
-                                                 const SweepRay& r, float& best_t, int& best_i) {
+                                                 const ExactRay& r, float& best_t, int& best_i) {
     const float a = plen2_3(mk3(r.dx, r.dy, r.dz));                                                // :253
     const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
     int e = 0;
@@ -94,51 +112,63 @@ __device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_ex
     n_list = 0;
 }
 
-// The sweep of RAYS rays per lane over `count` staged spheres (global indices index_base .. index_base+count).
+// The sweep of RAYS rays per lane over `count` spheres (global indices index_base .. index_base+count).
 //
-// Fast path per (sphere, ray), all lanes, no branch: the 12 FP32 operations of the discriminant plus ONE funnel shift
-// that appends the discriminant's sign bit to a 32-sphere mask word; one LDS.128 per sphere serves all RAYS rays of the
-// lane.  A set sign bit means disc < 0 (or disc = -0.0, which needs half_b = +-0 and then root1 = +-0 < 0.001: not a hit
-// either), so candidates are the clear bits.
+// Fast path per (sphere, ray), all lanes, no branch: the 8 FP32 operations of the conservative candidate filter
+// (rt_filter.h) plus ONE funnel shift that appends the filter value's sign bit to a 32-sphere mask word; one sphere
+// load serves all RAYS rays of the lane.  A set sign bit means "certainly disc < 0 in the reference's arithmetic".
 // Slow path (deferred, lane-parallel): mask words with a clear bit are pushed to a per-ray list in shared memory and
-// re-tested exactly (sqrt, root, range, `<=`) after the sweep, in sweep order — so the result is that of the
-// reference's sequential `update` over the object list.
+// re-tested with the reference's exact arithmetic (discriminant, sqrt, root, range, `<=`) after the sweep, in sweep
+// order — so the result is that of the reference's sequential `update` over the object list.
 // list layout: entry e of ray r of this thread at list[(r * CAP + e) * list_stride].  CAP >= number of 32-blocks
 // (CHECKED = false) removes the overflow test from the per-block path.
-template <int RAYS, int CAP, bool CHECKED>
-__device__ __forceinline__ void sweep_spheres(const float4* s_sph, const float4* __restrict__ g_exact, int count, int index_base,
-                                              uint2* list, int list_stride,
-                                              const SweepRay (&ray)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+template <int RAYS, int CAP, bool CHECKED, class SphSrc, class RaySrc>
+__device__ __forceinline__ void sweep_spheres(const SphSrc& sph, const RaySrc& rays, const float4* __restrict__ g_exact, int count,
+                                              int index_base, uint2* list, int list_stride, const FilterRay (&f)[RAYS],
+                                              float (&best_t)[RAYS], int (&best_i)[RAYS]) {
     int n_list[RAYS];
 #pragma unroll
     for (int r = 0; r < RAYS; r++) n_list[r] = 0;
     const int full = count & ~(SWEEP_BLOCK - 1);
-    for (int blk = 0; blk < full; blk += SWEEP_BLOCK) {
-        uint32_t mask[RAYS];
+    // The block loop holds no divergent inner loop (that would push its counters out of the uniform datapath): when some
+    // lane's list fills up, the whole warp leaves the loop on a vote, the full lists are drained, and the loop resumes.
+    int blk = 0;
+    for (;;) {
+        for (; blk < full; blk += SWEEP_BLOCK) {
+            uint32_t mask[RAYS];
 #pragma unroll
-        for (int r = 0; r < RAYS; r++) mask[r] = 0;
-        constexpr int UNROLL = SWEEP_BLOCK / RAYS;      // keep the unrolled body at ~450 instructions (instruction cache)
+            for (int r = 0; r < RAYS; r++) mask[r] = 0;
+            constexpr int UNROLL = SWEEP_BLOCK / RAYS;  // keep the unrolled body at ~350 instructions (instruction cache)
 #pragma unroll 1
-        for (int sub = 0; sub < SWEEP_BLOCK; sub += UNROLL) {
+            for (int sub = 0; sub < SWEEP_BLOCK; sub += UNROLL) {
 #pragma unroll
-            for (int j = 0; j < UNROLL; j++) {
-                float4 s = s_sph[blk + sub + j];                                                  // LDS.128 broadcast = Simd::splat
+                for (int j = 0; j < UNROLL; j++) {
+                    float4 s = sph.at(blk + sub + j);                                             // warp-uniform = Simd::splat
 #pragma unroll
-                for (int r = 0; r < RAYS; r++) {
-                    float q = filter_value(ray[r].f, s.x, s.y, s.z, s.w);                         // 8 FP32 instructions
-                    mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);                    // (mask << 1) | sign(q)
+                    for (int r = 0; r < RAYS; r++) {
+                        float q = filter_value(f[r], s.x, s.y, s.z, s.w);                         // 8 FP32 instructions
+                        mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);                // (mask << 1) | sign(q)
+                    }
                 }
             }
-        }
+            bool list_full = false;
 #pragma unroll
-        for (int r = 0; r < RAYS; r++) {
-            if (mask[r] != 0xffffffffu) {
-                list[(r * CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
-                n_list[r]++;
-                if (CHECKED && n_list[r] == CAP)
-                    drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+            for (int r = 0; r < RAYS; r++) {
+                if (mask[r] != 0xffffffffu) {
+                    list[(r * CAP + n_list[r]) * list_stride] = make_uint2(mask[r], (uint32_t)blk);
+                    n_list[r]++;
+                    list_full = list_full || n_list[r] == CAP;
+                }
             }
+            if (CHECKED && __any_sync(0xffffffffu, list_full)) { blk += SWEEP_BLOCK; break; }
         }
+        if (CHECKED) {
+#pragma unroll
+            for (int r = 0; r < RAYS; r++)
+                if (n_list[r] == CAP)
+                    drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], rays.load(r), best_t[r], best_i[r]);
+        }
+        if (blk >= full) break;
     }
     const int rem = count - full;                     // 0..31 spheres left: rolled loop, same arithmetic
     if (rem > 0) {
@@ -147,10 +177,10 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, const float4*
         for (int r = 0; r < RAYS; r++) mask[r] = 0;
 #pragma unroll 2
         for (int j = 0; j < rem; j++) {
-            float4 s = s_sph[full + j];
+            float4 s = sph.at(full + j);
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
-                float q = filter_value(ray[r].f, s.x, s.y, s.z, s.w);
+                float q = filter_value(f[r], s.x, s.y, s.z, s.w);
                 mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);
             }
         }
@@ -167,7 +197,99 @@ __device__ __forceinline__ void sweep_spheres(const float4* s_sph, const float4*
 #pragma unroll
     for (int r = 0; r < RAYS; r++)
         if (n_list[r] > 0)
-            drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], ray[r], best_t[r], best_i[r]);
+            drain_candidates(g_exact, index_base, list + r * CAP * list_stride, list_stride, n_list[r], rays.load(r), best_t[r], best_i[r]);
+}
+
+// The sweep of the parameter-space kernel (at most 32 blocks = 1024 spheres): same fast path, but a block loop with NO
+// data-dependent exit, so that ptxas keeps its counters and the sphere loads in the uniform datapath (LDCU -> uniform
+// registers).  Per ray a 32-bit `blocks` word gets one bit per 32-sphere block (bit b = block b has a candidate) and
+// the masks of the first CAP such blocks are stored (4 bytes each, list[(r * CAP + e) * list_stride]).  The drain
+// walks the set bits in block order: a stored mask is re-tested bit by bit, a block beyond the CAP-th (rare) is
+// re-tested whole.  Exact tests therefore run in sweep order, as PackedHitRecords::update needs (`<=`: last wins).
+template <int RAYS, int CAP, class SphSrc, class RaySrc>
+__device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const RaySrc& rays, const float4* __restrict__ g_exact, int count,
+                                                     uint32_t* list, int list_stride, const FilterRay (&f)[RAYS], float (&best_t)[RAYS],
+                                                     int (&best_i)[RAYS]) {
+    uint32_t blocks[RAYS];
+    int n_list[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) { blocks[r] = 0u; n_list[r] = 0; }
+    const int full = count & ~(SWEEP_BLOCK - 1);
+    uint32_t bit = 1u;
+    for (int blk = 0; blk < full; blk += SWEEP_BLOCK, bit <<= 1) {
+        uint32_t mask[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = 0;
+        constexpr int UNROLL = SWEEP_BLOCK / RAYS;
+#pragma unroll 1
+        for (int sub = 0; sub < SWEEP_BLOCK; sub += UNROLL) {
+#pragma unroll
+            for (int j = 0; j < UNROLL; j++) {
+                float4 s = sph.at(blk + sub + j);
+#pragma unroll
+                for (int r = 0; r < RAYS; r++) {
+                    float q = filter_value(f[r], s.x, s.y, s.z, s.w);
+                    mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            if (mask[r] != 0xffffffffu) {
+                if (n_list[r] < CAP) list[(r * CAP + n_list[r]) * list_stride] = mask[r];
+                n_list[r]++;
+                blocks[r] |= bit;
+            }
+        }
+    }
+    const int rem = count - full;                     // 0..31 spheres left: rolled loop, same arithmetic
+    if (rem > 0) {
+        uint32_t mask[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = 0;
+#pragma unroll 2
+        for (int j = 0; j < rem; j++) {
+            float4 s = sph.at(full + j);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                float q = filter_value(f[r], s.x, s.y, s.z, s.w);
+                mask[r] = __funnelshift_l(__float_as_uint(q), mask[r], 1);
+            }
+        }
+        const uint32_t fill = 0xffffffffu >> rem;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            uint32_t m = (mask[r] << (32 - rem)) | fill;
+            if (m != 0xffffffffu) {
+                if (n_list[r] < CAP) list[(r * CAP + n_list[r]) * list_stride] = m;
+                n_list[r]++;
+                blocks[r] |= bit;
+            }
+        }
+    }
+    // drain, lane-parallel, in sweep order
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) {
+        if (blocks[r] == 0u) continue;
+        const ExactRay ray = rays.load(r);
+        const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                      // src/objects.rs:253
+        const float inv_a = __fdiv_rn(1.0f, a);                                                    // :254
+        const uint32_t fill = rem > 0 ? (0xffffffffu >> rem) : 0u;                                  // never-candidates of a partial last block
+        uint32_t todo = blocks[r];
+        int e = 0;
+        while (todo) {
+            const int b = __ffs(todo) - 1;
+            todo &= todo - 1u;
+            const int cbase = b * SWEEP_BLOCK;
+            uint32_t cand = (e < CAP) ? ~list[(r * CAP + e) * list_stride] : (cbase == full ? ~fill : 0xffffffffu);
+            e++;
+            while (cand) {
+                const int j = __clz(cand);
+                cand &= ~(0x80000000u >> j);
+                test_candidate(ray, a, inv_a, __ldg(&g_exact[cbase + j]), cbase + j, best_t[r], best_i[r]);
+            }
+        }
+    }
 }
 
 // ---- K1 ----------------------------------------------------------------------------------------------------------
@@ -186,7 +308,8 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     bool live = i < n_rays;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
     if (live) { o = mk3(ox[i], oy[i], oz[i]); d = mk3(dx[i], dy[i], dz[i]); }
-    SweepRay ray[1] = {make_sweep_ray(o, d)};
+    ExactRay ray[1] = {make_exact_ray(o, d)};
+    FilterRay flt[1] = {make_filter(o, d)};
     float best_t[1] = {RTB_INF};                               // PackedHitRecords::default, src/objects.rs:121-134
     int best_i[1] = {-1};
     for (int begin = 0; begin < n_spheres; begin += tile) {
@@ -194,7 +317,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
         __syncthreads();
         stage_spheres(s_sph, g_flt, begin, count);
         __syncthreads();
-        sweep_spheres<1, LIST_CAP, true>(s_sph, g_sph + begin, count, begin, list, blockDim.x, ray, best_t, best_i);
+        sweep_spheres<1, LIST_CAP, true>(SmemSpheres{s_sph}, RegisterRays{ray}, g_sph + begin, count, begin, list, blockDim.x, flt, best_t, best_i);
     }
     if (live) {
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
@@ -222,169 +345,149 @@ struct TraceParams {
     unsigned long long* counters; // [0] paths, [1] segments
 };
 
+// TraceParams + the filter spheres themselves in the kernel's parameter space (constant bank 0), for scenes of at most
+// N spheres: the sweep then takes its sphere operand from uniform registers (ParamSpheres).
+template <int N>
+struct TraceParamsV {
+    TraceParams b;
+    float4 flt[N];
+};
+
+template <int N>
+struct ParamSpheres {
+    const TraceParamsV<N>& pv;
+    __device__ __forceinline__ float4 at(int i) const { return pv.flt[i]; }
+};
+
+constexpr uint32_t NO_ITEM = 0xffffffffu;
+
 // One path slot of a lane.  A slot owns one work item (a pixel and a contiguous range of its samples) at a time and
 // runs the samples one after another; the per-pixel sum `acc` is a private sum in sample order, so the image is
-// deterministic and needs no atomics.
+// deterministic and needs no atomics.  item = pixel * K + split (NO_ITEM: the slot is free).
 struct PathSlot {
     f3 o, d;                      // current ray (direction NOT normalised after scatter, src/ray.rs:13-18)
     f3 thr, acc;                  // path throughput (`color`, src/ray_tracing.rs:319) and the pixel's running sum
-    uint32_t pixel_id;            // row * W + col: Philox counter word 0
-    uint32_t out_off;             // float4 index into P.out
-    int s, s_end, n_s;            // next sample, end of the item's sample range, its length
+    uint32_t item;
+    int s;                        // next sample (global index)
     int bounce;
-    bool has_item, has_path;
+    bool has_path;
 };
 
-// Persistent kernel: grid = SMs x resident CTAs.  Every loop trip makes ONE closest-hit sweep for all slots of the
-// warp, then per slot: terminate (sky / depth limit) or keep the hit; finished items are written out and new ones
-// claimed with one atomic per warp; then ONE Philox block per slot feeds either the next camera ray or the scatter.
-// dynamic smem: n_spheres float4 + RAYS * CAP * THREADS uint2.  CAP = LIST_CAP_SMALL needs n_spheres <= 32 * CAP.
-template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const TraceParams P) {
-    extern __shared__ float4 smem4[];
-    float4* s_sph = smem4;
-    uint2* list = reinterpret_cast<uint2*>(smem4 + ((P.n_spheres + 1) & ~1)) + threadIdx.x;
-    stage_spheres(s_sph, P.filter, 0, P.n_spheres);
-    __syncthreads();
+__device__ __forceinline__ void slot_reset(PathSlot& q) {
+    q.o = mk3(0.f, 0.f, 0.f); q.d = mk3(0.f, 0.f, 1.f);
+    q.thr = mk3(1.f, 1.f, 1.f); q.acc = mk3(0.f, 0.f, 0.f);
+    q.item = NO_ITEM; q.s = 0; q.bounce = 0; q.has_path = false;
+}
 
-    const int W = P.cam.width;
-    const uint32_t n_pix = (uint32_t)(P.row_end - P.row_begin) * (uint32_t)W;
-    const uint32_t n_items = n_pix << P.splits_log2;          // host guarantees < 2^32
-    const uint32_t n_samples = (uint32_t)(P.sample_end - P.sample_begin);
-    const uint32_t first_pixel = (uint32_t)P.row_begin * (uint32_t)W;
-    const unsigned lane = threadIdx.x & 31u;
+// Launch-wide constants derived from TraceParams once per thread.
+struct TraceConsts {
+    int W;
+    uint32_t n_pix, n_items, n_samples, first_pixel, split_mask;
+};
 
-    PathSlot slot[RAYS];
-#pragma unroll
-    for (int r = 0; r < RAYS; r++) {
-        slot[r].o = mk3(0.f, 0.f, 0.f); slot[r].d = mk3(0.f, 0.f, 1.f);
-        slot[r].thr = mk3(1.f, 1.f, 1.f); slot[r].acc = mk3(0.f, 0.f, 0.f);
-        slot[r].pixel_id = 0; slot[r].out_off = 0; slot[r].s = 0; slot[r].s_end = 0; slot[r].n_s = 0; slot[r].bounce = 0;
-        slot[r].has_item = false; slot[r].has_path = false;
+__device__ __forceinline__ TraceConsts trace_consts(const TraceParams& P) {
+    TraceConsts c;
+    c.W = P.cam.width;
+    c.n_pix = (uint32_t)(P.row_end - P.row_begin) * (uint32_t)c.W;
+    c.n_items = c.n_pix << P.splits_log2;                     // host guarantees < 2^32
+    c.n_samples = (uint32_t)(P.sample_end - P.sample_begin);
+    c.first_pixel = (uint32_t)P.row_begin * (uint32_t)c.W;
+    c.split_mask = (1u << P.splits_log2) - 1u;
+    return c;
+}
+
+// Sample range [begin, end) of split `split` of an item.
+__device__ __forceinline__ int split_sample(const TraceParams& P, const TraceConsts& C, uint32_t split) {
+    return P.sample_begin + (int)(((unsigned long long)split * C.n_samples) >> P.splits_log2);
+}
+
+// One loop trip of one slot, steps 1-3 (warp-collective: every lane of the warp calls it together):
+//   1. after a sweep, terminate the path if it escaped (sky) or reached the depth limit (black);
+//   2. write a finished item out and claim a new one (one atomic per warp);
+//   3. ONE Philox block: the next camera sample (Camera::get_ray) or this bounce's scatter
+//      (finalize + Material::get_hit_result).
+__device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConsts& C, PathSlot& q, bool swept, float best_t, int best_i,
+                                          bool& exhausted, unsigned& n_segments, unsigned& n_paths, unsigned lane) {
+    // ---- 1. terminate (src/ray_tracing.rs:353-357, :365-370) ----
+    if (swept && q.has_path) {
+        n_segments++;
+        if (best_i < 0) {                              // hit the sky
+            f3 sk = sky(q.d);
+            q.acc = add3(q.acc, mk3(__fmul_rn(q.thr.x, sk.x), __fmul_rn(q.thr.y, sk.y), __fmul_rn(q.thr.z, sk.z)));
+            q.has_path = false;
+            q.s++;
+        } else if (q.bounce + 1 >= P.max_bounces) {    // still enabled after the last bounce => black (:370)
+            q.has_path = false;
+            q.s++;
+        }
     }
-    bool exhausted = false;
-    unsigned n_segments = 0, n_paths = 0;          // per-lane counts (a lane traces far fewer than 2^32 segments)
-    float best_t[RAYS];
-    int best_i[RAYS];
-    bool swept = false;
-
-    for (;;) {
-        // ---- 1. after a sweep: terminate paths that escaped or reached the depth limit ----
-        if (swept) {
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) {
-                PathSlot& q = slot[r];
-                if (q.has_path) {
-                    n_segments++;
-                    if (best_i[r] < 0) {                       // hit the sky (src/ray_tracing.rs:353-357, :365-369)
-                        f3 sk = sky(q.d);
-                        q.acc = add3(q.acc, mk3(__fmul_rn(q.thr.x, sk.x), __fmul_rn(q.thr.y, sk.y), __fmul_rn(q.thr.z, sk.z)));
-                        q.has_path = false;
-                        q.s++;
-                    } else if (q.bounce + 1 >= P.max_bounces) { // still enabled after the last bounce => black (:370)
-                        q.has_path = false;
-                        q.s++;
-                    }
-                }
-            }
+    // ---- 2. finished items are written out; new items are claimed with one atomic per warp ----
+    if (q.item != NO_ITEM && !q.has_path) {
+        const uint32_t split = q.item & C.split_mask, pix = q.item >> P.splits_log2;
+        const int s_end = split_sample(P, C, split + 1);
+        if (q.s >= s_end) {
+            const int n_s = s_end - split_sample(P, C, split);
+            const uint32_t out_off = (P.splits_log2 == 0) ? C.first_pixel + pix : split * C.n_pix + pix;
+            P.out[out_off] = make_float4(q.acc.x, q.acc.y, q.acc.z, (float)n_s);
+            q.item = NO_ITEM;
         }
-        // ---- 2. finished items are written out; new items are claimed with one atomic per warp ----
-        unsigned need_mask[RAYS];
-        int n_need = 0;
-#pragma unroll
-        for (int r = 0; r < RAYS; r++) {
-            PathSlot& q = slot[r];
-            if (q.has_item && !q.has_path && q.s >= q.s_end) {
-                P.out[q.out_off] = make_float4(q.acc.x, q.acc.y, q.acc.z, (float)q.n_s);
-                q.has_item = false;
-            }
-            need_mask[r] = __ballot_sync(0xffffffffu, !q.has_item && !exhausted);
-            n_need += __popc(need_mask[r]);
-        }
-        if (n_need) {
-            unsigned long long base64 = 0;
-            if (lane == 0) base64 = atomicAdd(P.work_counter, (unsigned long long)n_need);
-            base64 = __shfl_sync(0xffffffffu, base64, 0);
-            // items beyond n_items (< 2^32) saturate: the queue head only ever overshoots by the number of lanes
-            uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) {
-                PathSlot& q = slot[r];
-                if (!q.has_item && !exhausted) {
-                    uint32_t rank = __popc(need_mask[r] & ((1u << lane) - 1u));
-                    uint32_t item = base + rank;
-                    if (item >= base && item < n_items) {      // item = pixel * K + split: a warp works on neighbouring pixels
-                        uint32_t split = item & ((1u << P.splits_log2) - 1u), pix = item >> P.splits_log2;
-                        q.pixel_id = first_pixel + pix;
-                        q.out_off = (P.splits_log2 == 0) ? q.pixel_id : split * n_pix + pix;
-                        q.s = P.sample_begin + (int)(((unsigned long long)split * n_samples) >> P.splits_log2);
-                        q.s_end = P.sample_begin + (int)(((unsigned long long)(split + 1) * n_samples) >> P.splits_log2);
-                        q.n_s = q.s_end - q.s;
-                        q.acc = mk3(0.f, 0.f, 0.f);
-                        q.has_item = true;
-                        if (P.max_bounces <= 0) {              // `for _ in 0..0`: every ray stays enabled => black (:370)
-                            n_paths += (unsigned)q.n_s;
-                            q.s = q.s_end;
-                        }
-                    } else {
-                        exhausted = true;
-                    }
-                }
-                uint32_t adv = __popc(need_mask[r]);
-                base = (base + adv < base) ? 0xffffffffu : base + adv;
-            }
-        }
-        // ---- 3. one Philox block per slot: the next camera sample, or this bounce's scatter ----
-        bool any_path = false;
-#pragma unroll
-        for (int r = 0; r < RAYS; r++) {
-            PathSlot& q = slot[r];
-            const bool regen = q.has_item && !q.has_path && q.s < q.s_end;
-            if (regen || q.has_path) {
-                uint4 rnd = philox4x32_10(q.pixel_id, (uint32_t)q.s, regen ? RTB_DIM_CAMERA : 1u + (uint32_t)q.bounce, 0u, P.seed_lo, P.seed_hi);
-                if (regen) {                                   // Camera::get_ray, src/ray_tracing.rs:77-89
-                    uint32_t rowu = P.width_magic ? __umulhi(q.pixel_id, P.width_magic) : q.pixel_id;   // pixel / W
-                    if (rowu * (uint32_t)W > q.pixel_id) rowu--;                                       // estimate is q or q+1
-                    int row = (int)rowu, col = (int)(q.pixel_id - rowu * (uint32_t)W);
-                    camera_get_ray(P.cam, col, row, rnd, q.o, q.d);
-                    q.thr = mk3(1.f, 1.f, 1.f);
-                    q.bounce = 0;
-                    q.has_path = true;
-                    n_paths++;
-                } else {                                       // finalize + Material::get_hit_result (src/ray_tracing.rs:335-346)
-                    float4 sp = s_sph[best_i[r]];
-                    HitRec rec = finalize_hit(q.o, q.d, best_t[r], mk3(sp.x, sp.y, sp.z));
-                    f3 att, nd;
-                    scatter(__ldg(&P.mat_kind[best_i[r]]), __ldg(&P.mat[best_i[r]]), q.d, rec, rnd, att, nd);
-                    q.thr = mk3(__fmul_rn(q.thr.x, att.x), __fmul_rn(q.thr.y, att.y), __fmul_rn(q.thr.z, att.z));
-                    q.o = rec.p;
-                    q.d = nd;
-                    q.bounce++;
-                }
-            }
-            any_path = any_path || q.has_path;
-        }
-        if (!__any_sync(0xffffffffu, any_path)) {
-            bool idle = exhausted;
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) idle = idle && !slot[r].has_item;
-            if (__all_sync(0xffffffffu, idle)) break;
-            swept = false;
-            continue;                                          // items with an empty sample range: write out, claim again
-        }
-        // ---- 4. the closest-hit sweep (all lanes; a slot without a path sweeps its stale ray and the result is ignored)
-        SweepRay ray[RAYS];
-#pragma unroll
-        for (int r = 0; r < RAYS; r++) {
-            ray[r] = make_sweep_ray(slot[r].o, slot[r].d);
-            best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
-            best_i[r] = -1;
-        }
-        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(s_sph, P.spheres, P.n_spheres, 0, list, THREADS, ray, best_t, best_i);
-        swept = true;
     }
+    const unsigned need_mask = __ballot_sync(0xffffffffu, q.item == NO_ITEM && !exhausted);
+    if (need_mask) {
+        unsigned long long base64 = 0;
+        if (lane == 0) base64 = atomicAdd(P.work_counter, (unsigned long long)__popc(need_mask));
+        base64 = __shfl_sync(0xffffffffu, base64, 0);
+        // items beyond n_items (< 2^32) saturate: the queue head only ever overshoots by the number of lanes
+        const uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;
+        if (q.item == NO_ITEM && !exhausted) {
+            const uint32_t item = base + __popc(need_mask & ((1u << lane) - 1u));
+            if (item >= base && item < C.n_items) {    // item = pixel * K + split: a warp works on neighbouring pixels
+                q.item = item;
+                q.s = split_sample(P, C, item & C.split_mask);
+                q.acc = mk3(0.f, 0.f, 0.f);
+                if (P.max_bounces <= 0) {              // `for _ in 0..0`: every ray stays enabled => black (:370)
+                    const int s_end = split_sample(P, C, (item & C.split_mask) + 1);
+                    n_paths += (unsigned)(s_end - q.s);
+                    q.s = s_end;
+                }
+            } else {
+                exhausted = true;
+            }
+        }
+    }
+    // ---- 3. one Philox block: the next camera sample, or this bounce's scatter ----
+    bool regen = false;
+    uint32_t pixel_id = 0;
+    if (q.item != NO_ITEM) {
+        pixel_id = C.first_pixel + (q.item >> P.splits_log2);
+        regen = !q.has_path && q.s < split_sample(P, C, (q.item & C.split_mask) + 1);
+    }
+    if (regen || q.has_path) {
+        uint4 rnd = philox4x32_10(pixel_id, (uint32_t)q.s, regen ? RTB_DIM_CAMERA : 1u + (uint32_t)q.bounce, 0u, P.seed_lo, P.seed_hi);
+        if (regen) {                                   // Camera::get_ray, src/ray_tracing.rs:77-89
+            uint32_t rowu = P.width_magic ? __umulhi(pixel_id, P.width_magic) : pixel_id;   // pixel / W
+            if (rowu * (uint32_t)C.W > pixel_id) rowu--;                                    // estimate is q or q+1
+            int row = (int)rowu, col = (int)(pixel_id - rowu * (uint32_t)C.W);
+            camera_get_ray(P.cam, col, row, rnd, q.o, q.d);
+            q.thr = mk3(1.f, 1.f, 1.f);
+            q.bounce = 0;
+            q.has_path = true;
+            n_paths++;
+        } else {                                       // finalize + Material::get_hit_result (src/ray_tracing.rs:335-346)
+            float4 sp = __ldg(&P.spheres[best_i]);
+            HitRec rec = finalize_hit(q.o, q.d, best_t, mk3(sp.x, sp.y, sp.z));
+            f3 att, nd;
+            scatter(__ldg(&P.mat_kind[best_i]), __ldg(&P.mat[best_i]), q.d, rec, rnd, att, nd);
+            q.thr = mk3(__fmul_rn(q.thr.x, att.x), __fmul_rn(q.thr.y, att.y), __fmul_rn(q.thr.z, att.z));
+            q.o = rec.p;
+            q.d = nd;
+            q.bounce++;
+        }
+    }
+}
 
-    // ---- counters: one atomic pair per warp ----
+// Adds a warp's per-lane path/segment counts to the launch counters: one atomic pair per warp.
+__device__ __forceinline__ void flush_counters(const TraceParams& P, unsigned n_paths, unsigned n_segments, unsigned lane) {
     unsigned long long seg64 = n_segments, path64 = n_paths;
 #pragma unroll
     for (int sh = 16; sh > 0; sh >>= 1) {
@@ -397,6 +500,146 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     }
 }
 
+// K2, resident variant: path state in registers, filter spheres staged in shared memory.  Any scene that fits the
+// staging (up to ~11 000 spheres with one 1024-thread CTA per SM).
+// Persistent kernel: grid = SMs x resident CTAs.  Every loop trip runs slot_step for every slot of the lane, then makes
+// ONE closest-hit sweep for all slots of the warp.
+// dynamic smem: n_spheres float4 + RAYS * CAP * THREADS uint2.  CAP = LIST_CAP_SMALL needs n_spheres <= 32 * CAP.
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const TraceParams P) {
+    extern __shared__ float4 smem4[];
+    float4* s_sph = smem4;
+    uint2* list = reinterpret_cast<uint2*>(smem4 + ((P.n_spheres + 1) & ~1)) + threadIdx.x;
+    stage_spheres(s_sph, P.filter, 0, P.n_spheres);
+    __syncthreads();
+
+    const TraceConsts C = trace_consts(P);
+    const unsigned lane = threadIdx.x & 31u;
+    PathSlot slot[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
+    bool exhausted = false;
+    unsigned n_segments = 0, n_paths = 0;          // per-lane counts (a lane traces far fewer than 2^32 segments)
+    float best_t[RAYS];
+    int best_i[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) { best_t[r] = RTB_INF; best_i[r] = -1; }
+    bool swept = false;
+
+    for (;;) {
+        bool any_path = false, idle = true;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, n_segments, n_paths, lane);
+            any_path = any_path || slot[r].has_path;
+            idle = idle && slot[r].item == NO_ITEM;
+        }
+        if (!__any_sync(0xffffffffu, any_path)) {
+            if (__all_sync(0xffffffffu, idle && exhausted)) break;
+            swept = false;
+            continue;                                          // items with an empty sample range: write out, claim again
+        }
+        // the closest-hit sweep (all lanes; a slot without a path sweeps its stale ray and the result is ignored)
+        ExactRay ray[RAYS];
+        FilterRay flt[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            ray[r] = make_exact_ray(slot[r].o, slot[r].d);
+            flt[r] = make_filter(slot[r].o, slot[r].d);
+            best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
+            best_i[r] = -1;
+        }
+        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(SmemSpheres{s_sph}, RegisterRays{ray}, P.spheres, P.n_spheres, 0, list, THREADS, flt,
+                                                         best_t, best_i);
+        swept = true;
+    }
+    flush_counters(P, n_paths, n_segments, lane);
+}
+
+// K2, parameter-space variant (scenes of at most N spheres): the filter spheres are kernel parameters, so the sweep's
+// sphere operand sits in uniform registers, and every lane runs RAYS path slots whose state lives in SHARED memory
+// between trips (word w of slot r of thread t at st[(w * RAYS + r) * THREADS + t]: conflict-free).  The shading step
+// is a rolled loop over the slots (one copy of the code), the sweep is unrolled over them (one sphere load serves RAYS
+// filter evaluations), and only the RAYS x 8 filter constants are live in registers across the sweep.
+// dynamic smem: (SLOT_WORDS + CAP) * RAYS * THREADS words.  N <= 1024 (one bit per 32-sphere block in a 32-bit word).
+constexpr int SLOT_WORDS = 17;   // o 0-2, d 3-5, thr 6-8, acc 9-11, item 12, s 13, bounce|has_path<<31 14, best_t 15, best_i 16
+
+template <int RAYS, int THREADS>
+struct SmemRays {
+    const uint32_t* st;
+    __device__ __forceinline__ ExactRay load(int r) const {
+        ExactRay e;
+        e.ox = __uint_as_float(st[(0 * RAYS + r) * THREADS]); e.oy = __uint_as_float(st[(1 * RAYS + r) * THREADS]);
+        e.oz = __uint_as_float(st[(2 * RAYS + r) * THREADS]); e.dx = __uint_as_float(st[(3 * RAYS + r) * THREADS]);
+        e.dy = __uint_as_float(st[(4 * RAYS + r) * THREADS]); e.dz = __uint_as_float(st[(5 * RAYS + r) * THREADS]);
+        return e;
+    }
+};
+
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, int N>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __grid_constant__ TraceParamsV<N> PV) {
+    const TraceParams& P = PV.b;
+    extern __shared__ float4 smem4[];
+    uint32_t* st = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
+    uint32_t* list = reinterpret_cast<uint32_t*>(smem4) + SLOT_WORDS * RAYS * THREADS + threadIdx.x;
+    auto W = [&](int w, int r) -> uint32_t& { return st[(w * RAYS + r) * THREADS]; };
+    auto F = [&](int w, int r) -> float { return __uint_as_float(st[(w * RAYS + r) * THREADS]); };
+
+    const TraceConsts C = trace_consts(P);
+    const unsigned lane = threadIdx.x & 31u;
+#pragma unroll 1
+    for (int r = 0; r < RAYS; r++) {
+#pragma unroll
+        for (int w = 0; w < SLOT_WORDS; w++) W(w, r) = 0u;
+        W(5, r) = __float_as_uint(1.0f);                       // stale ray of an idle slot: d = (0,0,1)
+        W(12, r) = NO_ITEM;
+    }
+    bool exhausted = false;
+    unsigned n_segments = 0, n_paths = 0;
+    bool swept = false;
+
+    for (;;) {
+        bool any_path = false, idle = true;
+#pragma unroll 1
+        for (int r = 0; r < RAYS; r++) {
+            PathSlot q;
+            q.o = mk3(F(0, r), F(1, r), F(2, r)); q.d = mk3(F(3, r), F(4, r), F(5, r));
+            q.thr = mk3(F(6, r), F(7, r), F(8, r)); q.acc = mk3(F(9, r), F(10, r), F(11, r));
+            q.item = W(12, r); q.s = (int)W(13, r);
+            const uint32_t bw = W(14, r);
+            q.bounce = (int)(bw & 0x7fffffffu); q.has_path = (bw >> 31) != 0u;
+            slot_step(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, n_segments, n_paths, lane);
+            W(0, r) = __float_as_uint(q.o.x); W(1, r) = __float_as_uint(q.o.y); W(2, r) = __float_as_uint(q.o.z);
+            W(3, r) = __float_as_uint(q.d.x); W(4, r) = __float_as_uint(q.d.y); W(5, r) = __float_as_uint(q.d.z);
+            W(6, r) = __float_as_uint(q.thr.x); W(7, r) = __float_as_uint(q.thr.y); W(8, r) = __float_as_uint(q.thr.z);
+            W(9, r) = __float_as_uint(q.acc.x); W(10, r) = __float_as_uint(q.acc.y); W(11, r) = __float_as_uint(q.acc.z);
+            W(12, r) = q.item; W(13, r) = (uint32_t)q.s;
+            W(14, r) = (uint32_t)q.bounce | (q.has_path ? 0x80000000u : 0u);
+            any_path = any_path || q.has_path;
+            idle = idle && q.item == NO_ITEM;
+        }
+        if (!__any_sync(0xffffffffu, any_path)) {
+            if (__all_sync(0xffffffffu, idle && exhausted)) break;
+            swept = false;
+            continue;
+        }
+        FilterRay flt[RAYS];
+        float best_t[RAYS];
+        int best_i[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            flt[r] = make_filter(mk3(F(0, r), F(1, r), F(2, r)), mk3(F(3, r), F(4, r), F(5, r)));
+            best_t[r] = RTB_INF;
+            best_i[r] = -1;
+        }
+        sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<N>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS, flt, best_t,
+                                        best_i);
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) { W(15, r) = __float_as_uint(best_t[r]); W(16, r) = (uint32_t)best_i[r]; }
+        swept = true;
+    }
+    flush_counters(P, n_paths, n_segments, lane);
+}
 // ---- combine: accum[row range] = sum_k partial[k] in plane order (deterministic) -----------------------------------
 __global__ void __launch_bounds__(256) k_combine(const float4* __restrict__ partial, int splits, long long n_pix, float4* __restrict__ out) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

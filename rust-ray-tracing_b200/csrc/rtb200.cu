@@ -43,6 +43,8 @@ struct rtb200_ctx {
     // scene
     float4* d_spheres = nullptr;
     float4* d_filter = nullptr;
+    std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
+    std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsV<1024>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
     int n_spheres = 0;
@@ -58,7 +60,7 @@ struct rtb200_ctx {
     int64_t launches = 0;
     size_t max_optin_smem = 0;
     bool attrs_set = false;
-    int default_rays = 1;
+    int default_rays = 0;                              // 0 = choose by scene size
 };
 
 namespace {
@@ -142,31 +144,40 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     }
     if ((unsigned long long)n_pix * (unsigned long long)splits >= (1ull << 32) - 65536)
         return fail(RTB200_ERR_INVALID, "too many work items for one launch");
-    // Kernel variants: <threads, resident CTAs per SM, rays per lane, candidate-list capacity>.
-    constexpr int CS = rtb::LIST_CAP_SMALL, CG = rtb::LIST_CAP;
-    auto k_s1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CS>;     // <= 512 spheres: unchecked lists
-    auto k_s2 = rtb::k_trace_paths<SMALL_THREADS, 3, 2, CS>;
-    auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;     // up to ~2 000 spheres with four CTAs per SM
-    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;     // up to ~11 000 spheres, one CTA per SM
+    // Kernel variants.
+    //   v  : k_trace_paths_v<threads, CTAs/SM, rays per lane, list capacity, N> — filter spheres in parameter space, path
+    //        state in shared memory; scenes of at most N spheres (N = 512 or 1024: up to 16 KB of kernel parameters).
+    //   m1 : resident kernel, 256 threads x 4 CTAs/SM, spheres staged in shared memory (up to ~2 000 spheres).
+    //   l1 : resident kernel, 1024 threads x 1 CTA/SM (up to ~11 000 spheres).
+    constexpr int CG = rtb::LIST_CAP, CV = rtb::LIST_CAP_V, VT = 256, VR = 2;
+    auto k_v512 = rtb::k_trace_paths_v<VT, 4, VR, CV, 512>;
+    auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, 1024>;
+    auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
+    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
     if (!ctx->attrs_set) {
-        CU_TRY(cudaFuncSetAttribute(k_s1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_s2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_v512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_v1024, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
     }
     const int sms = ctx->prop.multiProcessorCount;
     const size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
-    const size_t smem_s1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1, CS);
-    const size_t smem_s2 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 2, CS);
+    const size_t smem_v = (size_t)(rtb::SLOT_WORDS + CV) * VR * VT * sizeof(uint32_t);
     const size_t smem_m1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1, CG);
     const size_t smem_l1 = trace_smem_bytes(P.n_spheres, LARGE_THREADS, 1, CG);
-    const bool small = P.n_spheres <= 32 * CS;
-    int variant = (p->flags & RTB200_FLAG_RAYS2) ? 2 : (p->flags & RTB200_FLAG_RAYS1) ? 1 : ctx->default_rays;
-    if (small && variant == 2 && (smem_s2 + 1024) * 3 <= per_sm) {
-        k_s2<<<sms * 3, SMALL_THREADS, smem_s2, st>>>(P);
-    } else if (small && (smem_s1 + 1024) * 4 <= per_sm) {
-        k_s1<<<sms * 4, SMALL_THREADS, smem_s1, st>>>(P);
+    int want = (p->flags & RTB200_FLAG_RAYS2) ? 2 : (p->flags & RTB200_FLAG_RAYS1) ? 1 : ctx->default_rays;
+    const bool use_v = want != 1 && P.n_spheres <= 1024 && (smem_v + 1024) * 4 <= per_sm;
+    if (use_v && P.n_spheres <= 512) {
+        auto* pv = reinterpret_cast<rtb::TraceParamsV<512>*>(ctx->h_params.data());
+        pv->b = P;
+        std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
+        k_v512<<<sms * 4, VT, smem_v, st>>>(*pv);
+    } else if (use_v) {
+        auto* pv = reinterpret_cast<rtb::TraceParamsV<1024>*>(ctx->h_params.data());
+        pv->b = P;
+        std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
+        k_v1024<<<sms * 4, VT, smem_v, st>>>(*pv);
     } else if ((smem_m1 + 1024) * 4 <= per_sm) {
         k_m1<<<sms * 4, SMALL_THREADS, smem_m1, st>>>(P);
     } else if (smem_l1 <= ctx->max_optin_smem) {
@@ -338,6 +349,7 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     CU_TRY(cudaMemcpy(ctx->d_mat, mat.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
     CU_TRY(cudaMemcpy(ctx->d_mat_kind, kind.data(), cnt * sizeof(int), cudaMemcpyHostToDevice));
     ctx->n_spheres = n;
+    ctx->h_filter.assign(flt.begin(), flt.begin() + n);
     return RTB200_OK;
 }
 
