@@ -220,7 +220,7 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
         uint32_t mask[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) mask[r] = 0;
-        constexpr int UNROLL = SWEEP_BLOCK / RAYS;
+        constexpr int UNROLL = RAYS == 1 ? 32 : RAYS == 2 ? 16 : 8;   // divides SWEEP_BLOCK; body of ~350 instructions
 #pragma unroll 1
         for (int sub = 0; sub < SWEEP_BLOCK; sub += UNROLL) {
 #pragma unroll

@@ -209,3 +209,43 @@ def test_errors_are_reported_not_fatal(rtb, renderer):
 def test_fp32_peak_probe(renderer):
     tf, ms = renderer.fp32_peak(500)
     assert 20.0 < tf < 100.0, tf
+
+
+def _tube_scene(rtb, n, radius=0.6, spacing=0.05):
+    """n overlapping spheres threaded on the z axis: a ray down the axis has candidates in EVERY 32-sphere block, which
+    overflows the per-ray candidate lists of every kernel variant (forced drains / whole-block re-tests)."""
+    S, M = rtb.Sphere, rtb.Material
+    mats = {"d": M.lambertian((0.6, 0.5, 0.4)), "m": M.metal((0.8, 0.8, 0.8), 0.1), "g": M.dielectric(1.5, False)}
+    names = ["d", "m", "g"]
+    return rtb.Scene.from_list([S((0.0, 0.0, -1.0 - spacing * i), radius, names[i % 3]) for i in range(n)], mats)
+
+
+@pytest.mark.parametrize("n", [300, 486, 700, 1500])
+def test_candidate_list_overflow_intersect(rtb, renderer, oracle, n):
+    scene = _tube_scene(rtb, n)
+    rng = np.random.default_rng(n)
+    m = 4000
+    o = np.zeros((m, 3), np.float32)
+    o[:, :2] = rng.normal(0, 0.2, size=(m, 2))
+    o[:, 2] = rng.uniform(0.5, 3.0, size=m)
+    d = np.zeros((m, 3), np.float32)
+    d[:, 2] = -1.0
+    d[:, :2] = rng.normal(0, 0.02, size=(m, 2))
+    d[m // 2:] *= -1.0          # half of the rays look away: every sphere is a candidate (the line hits), none is valid
+    idx, _ = _check_intersect(renderer, oracle, scene, o, d)
+    assert (idx[: m // 2] >= 0).mean() > 0.9 and np.all(idx[m // 2:] == -1)
+
+
+@pytest.mark.parametrize("rays", [1, 2])
+@pytest.mark.parametrize("n", [486, 700, 1500])
+def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays):
+    """Renders through every trace-kernel variant (parameter-space <= 512 / <= 1024 spheres, resident beyond) with rays
+    that carry far more candidate blocks than the per-ray lists hold."""
+    scene = _tube_scene(rtb, n)
+    cam = rtb.Camera(96, 54, 1.0, 40.0, (0.3, 0.2, 2.0), (0.0, 0.0, -10.0), (0.0, 1.0, 0.0), 0.0)
+    renderer.rays_per_lane = rays
+    img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 96, 54, 4, 12, camera=cam)
+    renderer.rays_per_lane = 0
+    assert np.abs(lin[..., :3].astype(np.float64) / 4 - ref_sum / 4).max() <= 1e-4
+    assert stat.segments == ref_seg
+    assert np.array_equal(img, ref_rgb)
