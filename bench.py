@@ -256,12 +256,13 @@ def run_ours(args):
     h2d = n_spheres * (16 + 16 + 4)
     d2h = W * H * 3
     if world == 1:
-        renderer.render(depth, spp_total, scene, cam)      # warm-up (allocations)
+        out_img = renderer.pinned_empty((H, W, 3), np.uint8)   # the caller's image buffer: pinned host memory
+        renderer.render(depth, spp_total, scene, cam, out=out_img)      # warm-up (allocations)
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             renderer.upload_scene(scene)                  # host -> device: the step's inputs
-            img, stat = renderer.render(depth, spp_total, scene, cam)   # device -> host: RGB8 image
+            img, stat = renderer.render(depth, spp_total, scene, cam, out=out_img)   # device -> host: RGB8 image
         e2e_s = (time.perf_counter() - t0) / e2e_steps
     else:
         barrier()
@@ -273,6 +274,9 @@ def run_ours(args):
         e2e_s = (time.perf_counter() - t0) / e2e_steps
     e2e_s = max_over_ranks(e2e_s)
     e2e_mpaths = paths / e2e_s * 1e-6
+    e2e_split = None
+    if world == 1:
+        e2e_split = {"trace_ms": stat.trace_ms, "resolve_ms": stat.resolve_ms, "d2h_ms": stat.d2h_ms, "call_ms": stat.duration * 1e3}
 
     # ---- CPU baseline (rank 0, N=1 only) -----------------------------------------------------------------
     cpu = None
@@ -280,6 +284,15 @@ def run_ours(args):
         res = cpu_reference_run(args.workload, 1, 0, 12.0)
         cpu = {"value": res["mpaths_s"], "unit": "Mpaths/s", "cores": res["cores"], "kind": "port", "sample": res["sample"],
                "sphere_tests_per_s": res["tests_s"]}
+
+    traffic = None       # DRAM bytes per launch of the dominant kernel, from the committed ncu capture of this workload
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(args.workload)
+        if t and not args.spp and world == 1:
+            traffic = t["dram_bytes_per_launch"]
+    except Exception:
+        traffic = None
 
     if rank == 0:
         line = {
@@ -292,12 +305,12 @@ def run_ours(args):
                        "seed": 1, "rays_per_lane": args.rays},
             "sphere_tests_per_s": tests_s, "segments_per_path": segs / max(paths, 1.0),
             "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": peak_tflops, "unit": "TFLOP/s",
-                         "frac": achieved_tflops / peak_tflops, "traffic": None,
+                         "frac": achieved_tflops / peak_tflops, "traffic": traffic,
                          "kernel": "k_trace_paths", "kernel_ms": trace_ms, "flop_per_test": FLOP_PER_TEST,
                          "peak_source": "K0 FFMA probe, measured live on this device",
                          "nominal_peak": nominal_tflops, "frac_of_nominal": achieved_tflops / nominal_tflops},
             "e2e": {"value": e2e_mpaths, "unit": "Mpaths/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_s * 1e3},
+                    "ms_per_step": e2e_s * 1e3, "last_call": e2e_split},
             "gpu_launches": launches,
             "clocks": clocks,
             "cpu_baseline": cpu,

@@ -111,6 +111,12 @@ const char* rtb200_last_error(void);
 /* Library / device facts: SM count, max SM clock (kHz), compiled arch.  Any pointer may be null. */
 int rtb200_device_info(rtb200_ctx* ctx, int32_t* sm_count, int32_t* sm_clock_khz, int32_t* cc_major, int32_t* cc_minor);
 
+/* Page-locked host memory for the image buffers handed to rtb200_render (the RgbImage the reference returns is plain
+ * heap memory, src/renderer.rs:376-384; with a pinned buffer the device->host copy of the result is one DMA).
+ * Any host pointer is accepted by rtb200_render; pinned ones are faster. */
+int rtb200_host_alloc(size_t bytes, void** out);
+void rtb200_host_free(void* p);
+
 /* Camera::new (src/ray_tracing.rs:27-62), evaluated in f64 on the host.  Pure host arithmetic (no device). */
 int rtb200_camera_init(rtb200_camera* out, int32_t image_width, int32_t image_height, double focal_length,
                        double view_angle_deg, const double center[3], const double look_at[3], const double up[3],

@@ -53,6 +53,8 @@ SYMBOLS = {
     "rtb200_create": (C.c_int, [C.c_int32, C.POINTER(_P)]),
     "rtb200_destroy": (None, [_P]),
     "rtb200_last_error": (C.c_char_p, []),
+    "rtb200_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(_P)]),
+    "rtb200_host_free": (None, [_P]),
     "rtb200_device_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "rtb200_camera_init": (C.c_int, [C.POINTER(Camera), C.c_int32, C.c_int32, C.c_double, C.c_double,
                                      C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double]),

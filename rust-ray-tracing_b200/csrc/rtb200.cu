@@ -41,6 +41,7 @@ struct rtb200_ctx {
     int device = 0;
     cudaDeviceProp prop{};
     // scene
+    void* d_scene = nullptr; size_t scene_capacity = 0;   // arena holding the four arrays below
     float4* d_spheres = nullptr;
     float4* d_filter = nullptr;
     std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
@@ -264,10 +265,21 @@ int rtb200_create(int32_t device, rtb200_ctx** out) {
 void rtb200_destroy(rtb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_spheres); cudaFree(c->d_filter); cudaFree(c->d_mat); cudaFree(c->d_mat_kind); cudaFree(c->d_counters);
+    cudaFree(c->d_scene); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     delete c;
+}
+
+int rtb200_host_alloc(size_t bytes, void** out) {
+    if (!out) return fail(RTB200_ERR_INVALID, "out is null");
+    *out = nullptr;
+    CU_TRY(cudaHostAlloc(out, bytes > 0 ? bytes : 1, cudaHostAllocDefault));
+    return RTB200_OK;
+}
+
+void rtb200_host_free(void* p) {
+    if (p) cudaFreeHost(p);
 }
 
 int rtb200_device_info(rtb200_ctx* ctx, int32_t* sm_count, int32_t* sm_clock_khz, int32_t* cc_major, int32_t* cc_minor) {
@@ -337,17 +349,27 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         kind[i] = m.kind | ((m.kind == RTB200_DIELECTRIC && m.hollow) ? RTB_HOLLOW_BIT : 0);
     }
     CU_TRY(cudaSetDevice(ctx->device));
-    cudaFree(ctx->d_spheres); cudaFree(ctx->d_filter); cudaFree(ctx->d_mat); cudaFree(ctx->d_mat_kind);
-    ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
-    size_t cnt = (size_t)(n > 0 ? n : 1);
-    CU_TRY(cudaMalloc(&ctx->d_spheres, cnt * sizeof(float4)));
-    CU_TRY(cudaMalloc(&ctx->d_filter, cnt * sizeof(float4)));
-    CU_TRY(cudaMalloc(&ctx->d_mat, cnt * sizeof(float4)));
-    CU_TRY(cudaMalloc(&ctx->d_mat_kind, cnt * sizeof(int)));
-    CU_TRY(cudaMemcpy(ctx->d_spheres, sph.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(ctx->d_filter, flt.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(ctx->d_mat, mat.data(), cnt * sizeof(float4), cudaMemcpyHostToDevice));
-    CU_TRY(cudaMemcpy(ctx->d_mat_kind, kind.data(), cnt * sizeof(int), cudaMemcpyHostToDevice));
+    // One device arena [spheres | filter | materials | kinds], reused while it is large enough, filled by ONE copy.
+    const size_t cnt = (size_t)(n > 0 ? n : 1);
+    const size_t bytes = cnt * (3 * sizeof(float4) + sizeof(int));
+    if (ctx->scene_capacity < bytes) {
+        cudaFree(ctx->d_scene);
+        ctx->d_scene = nullptr; ctx->scene_capacity = 0;
+        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
+        CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
+        ctx->scene_capacity = bytes;
+    }
+    std::vector<unsigned char> host(bytes);
+    std::memcpy(host.data(), sph.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + cnt * sizeof(float4), flt.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + 2 * cnt * sizeof(float4), mat.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + 3 * cnt * sizeof(float4), kind.data(), cnt * sizeof(int));
+    CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
+    unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
+    ctx->d_spheres = reinterpret_cast<float4*>(base);
+    ctx->d_filter = reinterpret_cast<float4*>(base + cnt * sizeof(float4));
+    ctx->d_mat = reinterpret_cast<float4*>(base + 2 * cnt * sizeof(float4));
+    ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);
     return RTB200_OK;

@@ -57,8 +57,23 @@ class CudaRenderer(Renderer):
         self.seed = int(seed)
         self._scene_id = None
         self._keep = None
+        self._pinned = []
+
+    def pinned_empty(self, shape, dtype) -> np.ndarray:
+        """A numpy array over page-locked host memory (rtb200_host_alloc) for `render(..., out=...)`: the device->host
+        copy of the image is then a single DMA.  The memory lives until close()."""
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape)) * dt.itemsize
+        p = C.c_void_p()
+        _abi.check(_abi.lib.rtb200_host_alloc(n, C.byref(p)))
+        self._pinned.append(p)
+        buf = (C.c_uint8 * max(n, 1)).from_address(p.value)
+        return np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
 
     def close(self) -> None:
+        for p in getattr(self, "_pinned", []):
+            _abi.lib.rtb200_host_free(p)
+        self._pinned = []
         if getattr(self, "_ctx", None) is not None and self._ctx:
             _abi.lib.rtb200_destroy(self._ctx)
             self._ctx = C.c_void_p()
@@ -100,13 +115,19 @@ class CudaRenderer(Renderer):
 
     # ---- Renderer::render -------------------------------------------------------------------------------------
     def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera, *, want_linear: bool = False,
-               sample_range=None, row_range=None):
+               sample_range=None, row_range=None, out: Optional[np.ndarray] = None):
         """Renderer::render (src/renderer.rs:38-40).  Returns (image[H,W,3] uint8, RenderStat); with want_linear=True
-        returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat)."""
+        returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat).  `out`: optional [H,W,3] uint8 buffer to
+        receive the image (e.g. from pinned_empty) instead of a fresh array."""
         if self._scene_id != id(scene):
             self.upload_scene(scene)
         W, H = camera.image_width(), camera.image_height()
-        img = np.empty((H, W, 3), dtype=np.uint8)
+        if out is not None:
+            if out.shape != (H, W, 3) or out.dtype != np.uint8 or not out.flags.c_contiguous:
+                raise ValueError("out must be a C-contiguous [H,W,3] uint8 array")
+            img = out
+        else:
+            img = np.empty((H, W, 3), dtype=np.uint8)
         lin = np.empty((H, W, 4), dtype=np.float32) if want_linear else None
         st = _abi.Stats()
         p = self._params(max_bounces, samples_per_pixel, camera, sample_range, row_range)
