@@ -180,7 +180,7 @@ def run_ours(args):
     cam = rtb.Camera.default(W, H)
     renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays)
     tracer = dmod.CudaTracer(renderer, scene)
-    sharded = dmod.ShardedRenderer(tracer, mode="samples")
+    sharded = dmod.ShardedRenderer(tracer, mode="samples", exchange=args.exchange)
     info = renderer.device_info()
 
     def barrier():
@@ -219,19 +219,12 @@ def run_ours(args):
     barrier()
     ev0.record()
     out = None
+    step = [0]
+    sharded.on_trace = lambda phase: trace_ev[step[0]][phase].record()   # the trace kernel alone, on its own stream (roofline)
     for i in range(args.steps):
-        # the trace kernel alone, timed on the stream it is launched on (for the roofline)
-        H_ = cam.image_height()
-        if sharded._accum is None:
-            sharded._accum = tracer.new_accum(cam)
-        sr, rr = sharded.shard(spp_total, H_)
-        trace_ev[i][0].record()
-        tracer.trace(sharded._accum, depth, spp_total, cam, sr, rr)
-        trace_ev[i][1].record()
-        if world > 1:
-            dist.reduce(sharded._accum, dst=0, op=dist.ReduceOp.SUM)
-        if rank == 0:
-            out = tracer.resolve(sharded._accum, spp_total)
+        step[0] = i
+        out = sharded.render_device(depth, spp_total, cam)               # trace + exchange + resolve
+    sharded.on_trace = None
     ev1.record()
     barrier()
     clocks = sampler.stop() if rank == 0 else None
@@ -300,7 +293,9 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {gen} {W}x{H}, {spp_per_gpu} spp per GPU ({spp_total} spp total), depth {depth}",
-                       "n_spheres": n_spheres, "sharding": "sample-range + NCCL reduce(sum) to rank 0" if world > 1 else "single GPU",
+                       "n_spheres": n_spheres, "sharding": ("sample-range; exchange = " + {"p2p": "fused NVLink peer-memory reduce+resolve kernel (CUDA IPC), two 4-byte all-reduces as barriers",
+                                                                   "nccl": "NCCL reduce(sum) to rank 0 + resolve"}[sharded.exchange_in_use()])
+                       if world > 1 else "single GPU",
                        "l2": "no reuse across steps: each step re-traces from the camera; inputs are KBs, the framebuffer is written once",
                        "seed": 1, "rays_per_lane": args.rays},
             "sphere_tests_per_s": tests_s, "segments_per_path": segs / max(paths, 1.0),
@@ -330,6 +325,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

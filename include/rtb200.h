@@ -161,6 +161,31 @@ int rtb200_intersect_batch_device(rtb200_ctx* ctx, const float* ox, const float*
                                   const float* dy, const float* dz, const uint8_t* enabled, int64_t n,
                                   int32_t* hit_index, float* hit_t, void* stream);
 
+/* ---- multi-GPU exchange over NVLink peer memory (one process per GPU) ---------------------------------------
+ * The reference gathers tile results over a channel and assembles the image on the main thread
+ * (src/renderer.rs:300-365, :376-384).  Across GPUs the equivalent is ONE kernel per rank that reads every rank's
+ * partial accumulation image for its slice of pixels straight from peer memory, sums them in rank order, and writes
+ * the quantised RGB8 slice — into the root rank's image, again through peer memory.  No staging copy, no separate
+ * reduce pass. */
+
+/* Plain cudaMalloc / cudaFree of an exchange buffer (IPC handles need whole allocations). */
+int rtb200_device_alloc(rtb200_ctx* ctx, size_t bytes, void** dev_out);
+int rtb200_device_free(rtb200_ctx* ctx, void* dev);
+
+#define RTB200_IPC_HANDLE_BYTES 64
+/* cudaIpcGetMemHandle / cudaIpcOpenMemHandle / cudaIpcCloseMemHandle for a buffer from rtb200_device_alloc. */
+int rtb200_ipc_export(rtb200_ctx* ctx, void* dev, uint8_t handle_out[RTB200_IPC_HANDLE_BYTES]);
+int rtb200_ipc_open(rtb200_ctx* ctx, const uint8_t handle[RTB200_IPC_HANDLE_BYTES], void** dev_out);
+int rtb200_ipc_close(rtb200_ctx* ctx, void* dev);
+
+#define RTB200_MAX_PEERS 16
+/* Fused reduce + resolve for pixels [pixel_begin, pixel_end): rgb8_dev[3*p..] = quantise(sum_k accum_ptrs[k][p] / spp),
+ * the sum taken in array order (deterministic).  accum_ptrs: n_peers device pointers (own buffer and peers' buffers
+ * opened with rtb200_ipc_open), each image_width*image_height float4.  rgb8_dev: base of a WHOLE-image RGB8 buffer
+ * (local or a peer's).  Asynchronous on `stream`. */
+int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin,
+                                int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* stream);
+
 /* Device counters of the last trace on this context (valid after the stream has been synchronised). */
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
 

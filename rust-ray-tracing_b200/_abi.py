@@ -64,6 +64,12 @@ SYMBOLS = {
     "rtb200_trace_device": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P]),
     "rtb200_resolve_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_intersect_batch_device": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
+    "rtb200_device_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),
+    "rtb200_device_free": (C.c_int, [_P, _P]),
+    "rtb200_ipc_export": (C.c_int, [_P, _P, _P]),
+    "rtb200_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
+    "rtb200_ipc_close": (C.c_int, [_P, _P]),
+    "rtb200_resolve_peers_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtb200_launch_count": (C.c_int64, [_P]),
     "rtb200_fp32_peak": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

@@ -675,6 +675,53 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
     }
 }
 
+// ---- K3p: fused peer reduce + resolve.  Each thread owns 4 consecutive pixels: it loads their float4 partial sums from
+// every rank's accumulation image (its own HBM and, over NVLink, the peers'), adds them in rank order, and stores 12
+// bytes of RGB8 (possibly into a peer's image).  All loads of a thread are issued before the first add.
+struct PeerPtrs { const float4* p[16]; };
+
+__global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ PeerPtrs peers, int n_peers, long long pixel_begin, long long pixel_end, float spp,
+                                                       uint8_t* __restrict__ rgb8) {
+    long long p0 = pixel_begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (p0 >= pixel_end) return;
+    const int n = (int)((pixel_end - p0) < 4 ? (pixel_end - p0) : 4);
+    float4 acc[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int g = 0; g < n_peers; g += 4) {                   // four peers' loads in flight at a time
+        float4 v[4][4];
+#pragma unroll
+        for (int gg = 0; gg < 4; gg++)
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                v[gg][k] = (g + gg < n_peers && k < n) ? peers.p[g + gg][p0 + k] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int gg = 0; gg < 4; gg++)
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                if (g + gg < n_peers) {
+                    acc[k].x = __fadd_rn(acc[k].x, v[gg][k].x); acc[k].y = __fadd_rn(acc[k].y, v[gg][k].y);
+                    acc[k].z = __fadd_rn(acc[k].z, v[gg][k].z); acc[k].w = __fadd_rn(acc[k].w, v[gg][k].w);
+                }
+            }
+    }
+    uint32_t b[12];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        b[3 * k + 0] = quantise(__fdiv_rn(acc[k].x, spp));          // pixel = sum / spp, src/renderer.rs:161
+        b[3 * k + 1] = quantise(__fdiv_rn(acc[k].y, spp));
+        b[3 * k + 2] = quantise(__fdiv_rn(acc[k].z, spp));
+    }
+    if (n == 4 && (((reinterpret_cast<uintptr_t>(rgb8) + (uintptr_t)(p0 * 3)) & 3) == 0)) {
+        uint32_t* o32 = reinterpret_cast<uint32_t*>(rgb8 + p0 * 3);
+        o32[0] = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+        o32[1] = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
+        o32[2] = b[8] | (b[9] << 8) | (b[10] << 16) | (b[11] << 24);
+    } else {
+        for (int k = 0; k < 3 * n; k++) rgb8[p0 * 3 + k] = (uint8_t)b[k];
+    }
+}
+
 // ---- K0: FP32 FMA peak probe ----------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024, 1) k_fp32_peak(float* out, int iters, float seed) {
     float acc[8];

@@ -479,6 +479,71 @@ int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_par
     return RTB200_OK;
 }
 
+int rtb200_device_alloc(rtb200_ctx* ctx, size_t bytes, void** dev_out) {
+    if (!ctx || !dev_out) return fail(RTB200_ERR_INVALID, "null argument");
+    *dev_out = nullptr;
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(cudaMalloc(dev_out, bytes > 0 ? bytes : 1));
+    CU_TRY(cudaMemset(*dev_out, 0, bytes > 0 ? bytes : 1));
+    return RTB200_OK;
+}
+
+int rtb200_device_free(rtb200_ctx* ctx, void* dev) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(cudaFree(dev));
+    return RTB200_OK;
+}
+
+int rtb200_ipc_export(rtb200_ctx* ctx, void* dev, uint8_t handle_out[RTB200_IPC_HANDLE_BYTES]) {
+    if (!ctx || !dev || !handle_out) return fail(RTB200_ERR_INVALID, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RTB200_IPC_HANDLE_BYTES, "IPC handle size");
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    CU_TRY(cudaIpcGetMemHandle(&h, dev));
+    std::memcpy(handle_out, &h, sizeof h);
+    return RTB200_OK;
+}
+
+int rtb200_ipc_open(rtb200_ctx* ctx, const uint8_t handle[RTB200_IPC_HANDLE_BYTES], void** dev_out) {
+    if (!ctx || !handle || !dev_out) return fail(RTB200_ERR_INVALID, "null argument");
+    *dev_out = nullptr;
+    CU_TRY(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    CU_TRY(cudaIpcOpenMemHandle(dev_out, h, cudaIpcMemLazyEnablePeerAccess));
+    return RTB200_OK;
+}
+
+int rtb200_ipc_close(rtb200_ctx* ctx, void* dev) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    CU_TRY(cudaSetDevice(ctx->device));
+    CU_TRY(cudaIpcCloseMemHandle(dev));
+    return RTB200_OK;
+}
+
+int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin, int64_t pixel_end,
+                                int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+    if (!ctx || !accum_ptrs || !rgb8_dev) return fail(RTB200_ERR_INVALID, "null argument");
+    if (n_peers < 1 || n_peers > RTB200_MAX_PEERS) return fail(RTB200_ERR_INVALID, "n_peers must be 1.." + std::to_string(RTB200_MAX_PEERS));
+    if (pixel_begin < 0 || pixel_end < pixel_begin || samples_per_pixel <= 0) return fail(RTB200_ERR_INVALID, "bad pixel range or sample count");
+    rtb::PeerPtrs pp;
+    for (int k = 0; k < RTB200_MAX_PEERS; k++) pp.p[k] = nullptr;
+    for (int k = 0; k < n_peers; k++) {
+        if (!accum_ptrs[k]) return fail(RTB200_ERR_INVALID, "null peer pointer");
+        pp.p[k] = static_cast<const float4*>(accum_ptrs[k]);
+    }
+    if (pixel_end == pixel_begin) return RTB200_OK;
+    CU_TRY(cudaSetDevice(ctx->device));
+    const long long quads = (pixel_end - pixel_begin + 3) / 4;
+    const int blocks = (int)((quads + 255) / 256);
+    rtb::k_resolve_peers<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(pp, n_peers, pixel_begin, pixel_end, (float)samples_per_pixel,
+                                                                               static_cast<uint8_t*>(rgb8_dev));
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    return RTB200_OK;
+}
+
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
     CU_TRY(cudaSetDevice(ctx->device));

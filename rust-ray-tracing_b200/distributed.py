@@ -7,8 +7,19 @@ balance; the Philox counter carries the global sample index, so the image does n
 summation order).  Secondary is by ROW RANGE — disjoint rows, zero elsewhere — the analogue of the reference's tile
 queue (src/renderer.rs:254-266).
 
+Two exchanges are implemented (ShardedRenderer(exchange=...)):
+
+  "p2p"  (default where it works) — NVLink peer memory, no reduce pass: every rank's accumulation image is a plain
+         cudaMalloc buffer exported with CUDA IPC; after the trace, rank g runs ONE kernel (rtb200_resolve_peers_device)
+         that, for its slice of the pixels, loads the partial sums of ALL ranks straight from peer memory, adds them in
+         rank order (deterministic), quantises, and stores the RGB8 slice directly into rank dst's image.  The only
+         torch.distributed calls are two 4-byte all-reduces used as stream-ordered barriers (before: every trace has
+         finished; after: every slice has landed).
+  "nccl" — reduce(SUM) of the float4 image onto dst, then the resolve kernel there (the baseline; also the fallback
+         when IPC / peer access is unavailable).
+
 torch is plumbing here: device memory, the stream, and the collective.  The tracer object does the work; the CUDA
-tracer calls the C ABI (rtb200_trace_device / rtb200_resolve_device).
+tracer calls the C ABI (rtb200_trace_device / rtb200_resolve_device / rtb200_resolve_peers_device).
 """
 from __future__ import annotations
 
@@ -43,6 +54,13 @@ class CudaTracer:
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
         self.r.trace_device(max_bounces, spp_total, camera, accum.data_ptr(), stream, sample_range, row_range)
 
+    def new_peer_exchange(self, dist, group, world, rank, height, width):
+        return PeerExchange(self, dist, group, world, rank, height, width)
+
+    def resolve_peers(self, accum_ptrs, pixel_begin, pixel_end, spp_total, rgb8_ptr):
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        self.r.resolve_peers_device(accum_ptrs, pixel_begin, pixel_end, spp_total, rgb8_ptr, stream)
+
     def resolve(self, accum, spp_total):
         n = accum.shape[0] * accum.shape[1]
         out = self.torch.empty((accum.shape[0], accum.shape[1], 3), dtype=self.torch.uint8, device=self.device)
@@ -51,16 +69,89 @@ class CudaTracer:
         return out
 
 
+class DeviceBuffer:
+    """A raw device allocation (rtb200_device_alloc) that torch can wrap without copying (__cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, shape, typestr: str, owner=None):
+        self.ptr = int(ptr)
+        self.shape = tuple(shape)
+        self.typestr = typestr
+        self.owner = owner
+
+    def data_ptr(self) -> int:
+        return self.ptr
+
+    @property
+    def __cuda_array_interface__(self):
+        return {"shape": self.shape, "typestr": self.typestr, "data": (self.ptr, False), "version": 2, "strides": None}
+
+
+class PeerExchange:
+    """The NVLink peer-memory exchange state of one rank for one image size: its own accumulation image and RGB8 image
+    (plain device allocations), and every peer's, opened through CUDA IPC."""
+
+    def __init__(self, tracer, dist, group, world: int, rank: int, height: int, width: int):
+        import ctypes as C
+        torch = tracer.torch
+        self.tracer, self.world, self.rank, self.H, self.W = tracer, world, rank, height, width
+        r = tracer.r
+        n_pix = height * width
+        self.accum = DeviceBuffer(r.device_alloc(n_pix * 16), (height, width, 4), "<f4")
+        self.rgb8 = DeviceBuffer(r.device_alloc(n_pix * 3 + 16), (height, width, 3), "|u1")
+        mine = torch.tensor(list(r.ipc_export(self.accum.ptr)) + list(r.ipc_export(self.rgb8.ptr)), dtype=torch.uint8, device=tracer.device)
+        every = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine, group=group)
+        self.peer_accum, self.peer_rgb8, self._opened = [], [], []
+        ok = 1
+        for g, h in enumerate(every):
+            if g == rank:
+                self.peer_accum.append(self.accum.ptr)
+                self.peer_rgb8.append(self.rgb8.ptr)
+                continue
+            hb = bytes(h.cpu().tolist())
+            try:
+                a = r.ipc_open(hb[:64])
+                self._opened.append(a)
+                b = r.ipc_open(hb[64:])
+                self._opened.append(b)
+                self.peer_accum.append(a)
+                self.peer_rgb8.append(b)
+            except Exception:
+                ok = 0
+                self.peer_accum.append(0)
+                self.peer_rgb8.append(0)
+        flag = torch.tensor([ok], dtype=torch.int32, device=tracer.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        self.usable = bool(flag.item())
+
+    def close(self):
+        for p in self._opened:
+            try:
+                self.tracer.r.ipc_close(p)
+            except Exception:
+                pass
+        self._opened = []
+        for b in (self.accum, self.rgb8):
+            if b is not None and b.ptr:
+                self.tracer.r.device_free(b.ptr)
+                b.ptr = 0
+
+
 class ShardedRenderer:
     """Renderer::render (src/renderer.rs:38-40) across the ranks of a torch.distributed group.
 
     Every rank calls render(); rank `dst` gets the RGB8 image, the others get None.
     """
 
-    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0):
+    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0, exchange: str = "auto"):
         import torch.distributed as dist
         if mode not in ("samples", "rows"):
             raise ValueError("mode must be 'samples' or 'rows'")
+        if exchange not in ("auto", "p2p", "nccl"):
+            raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        self.exchange = exchange
+        self._peer = None
+        self.on_trace = None      # optional callback(phase): phase 0 just before, 1 just after the trace kernel is queued (timing hooks)
         self.dist = dist
         self.tracer = tracer
         self.group = group
@@ -75,9 +166,67 @@ class ShardedRenderer:
             return shard_range(spp_total, self.world, self.rank), (0, height)
         return (0, spp_total), shard_range(height, self.world, self.rank)
 
+    # ---- the NVLink peer-memory exchange ------------------------------------------------------------------
+    def _peer_exchange(self, camera):
+        """The PeerExchange for this image size, or None when the exchange is "nccl", the world is 1, the tracer has
+        no peer support (CPU test double), or IPC / peer access failed on some rank (then every rank falls back)."""
+        if self.world == 1 or self.exchange == "nccl" or not hasattr(self.tracer, "resolve_peers"):
+            return None
+        H, W = camera.image_height(), camera.image_width()
+        if self._peer is not None and (self._peer.H, self._peer.W) != (H, W):
+            self._peer.close()
+            self._peer = None
+        if self._peer is None:
+            self._peer = self.tracer.new_peer_exchange(self.dist, self.group, self.world, self.rank, H, W)
+            if not self._peer.usable:
+                if self.exchange == "p2p":
+                    raise RuntimeError("exchange='p2p' requested but CUDA IPC / peer access is not available on every rank")
+                self._peer.close()
+                self.exchange = "nccl"
+                self._peer = None
+                return None
+            self._flag = self.tracer.torch.zeros(1, dtype=self.tracer.torch.float32, device=self.tracer.device)
+        return self._peer
+
+    def _trace(self, accum, max_bounces, spp_total, camera, sample_range, row_range):
+        if self.on_trace:
+            self.on_trace(0)
+        self.tracer.trace(accum, max_bounces, spp_total, camera, sample_range, row_range)
+        if self.on_trace:
+            self.on_trace(1)
+
+    def exchange_in_use(self) -> str:
+        return "p2p" if self._peer is not None else ("none" if self.world == 1 else "nccl")
+
+    def _stream_barrier(self):
+        """Stream-ordered barrier: a 4-byte all-reduce.  It starts after this rank's queued kernels and the kernels queued
+        after it start only when every rank has reached it."""
+        self.dist.all_reduce(self._flag, group=self.group)
+
+    def _render_device_p2p(self, px, max_bounces: int, spp_total: int, camera):
+        H, W = px.H, px.W
+        sample_range, row_range = self.shard(spp_total, H)
+        self._trace(px.accum, max_bounces, spp_total, camera, sample_range, row_range)
+        self._stream_barrier()                                   # every rank's partial image is complete
+        if self.mode == "samples":
+            # rank g reduces + resolves its contiguous slice of the pixels from ALL ranks' partial images
+            p0, p1 = shard_range(H * W, self.world, self.rank)
+            p0, p1 = (p0 + 3) // 4 * 4 if self.rank else 0, (p1 + 3) // 4 * 4 if self.rank + 1 < self.world else H * W
+            self.tracer.resolve_peers(px.peer_accum, p0, p1, spp_total, px.peer_rgb8[self.dst])
+        else:
+            # disjoint rows: every rank resolves its own rows from its own image, straight into dst's image
+            self.tracer.resolve_peers([px.accum.ptr], row_range[0] * W, row_range[1] * W, spp_total, px.peer_rgb8[self.dst])
+        self._stream_barrier()                                   # every slice has landed in dst's image
+        if self.rank == self.dst:
+            return self.tracer.torch.as_tensor(px.rgb8, device=self.tracer.device)
+        return None
+
     def render_device(self, max_bounces: int, spp_total: int, camera):
-        """Trace the local shard, reduce, resolve on dst.  Returns the device RGB8 tensor on dst (None elsewhere).
+        """Trace the local shard, exchange, resolve.  Returns the device RGB8 tensor on dst (None elsewhere).
         Asynchronous with respect to the host (everything is queued on the current stream / NCCL stream)."""
+        px = self._peer_exchange(camera)
+        if px is not None:
+            return self._render_device_p2p(px, max_bounces, spp_total, camera)
         H = camera.image_height()
         if self._accum is None or tuple(self._accum.shape[:2]) != (H, camera.image_width()):
             self._accum = self.tracer.new_accum(camera)
@@ -85,7 +234,7 @@ class ShardedRenderer:
         sample_range, row_range = self.shard(spp_total, H)
         if self.mode == "rows":
             accum.zero_()     # rows outside the shard must contribute zero to the sum
-        self.tracer.trace(accum, max_bounces, spp_total, camera, sample_range, row_range)
+        self._trace(accum, max_bounces, spp_total, camera, sample_range, row_range)
         if self.world > 1:
             self.dist.reduce(accum, dst=self.dst, op=self.dist.ReduceOp.SUM, group=self.group)
         if self.rank == self.dst:

@@ -172,6 +172,36 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_intersect_batch_device(self._ctx, ox, oy, oz, dx, dy, dz, C.c_void_p(enabled_ptr) if enabled_ptr else None,
                                                           int(n), C.c_void_p(idx_ptr), C.c_void_p(t_ptr), C.c_void_p(stream)))
 
+    # ---- multi-GPU exchange buffers (NVLink peer memory through CUDA IPC) -------------------------------------
+    def device_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        _abi.check(_abi.lib.rtb200_device_alloc(self._ctx, int(nbytes), C.byref(p)))
+        return int(p.value)
+
+    def device_free(self, ptr: int) -> None:
+        _abi.check(_abi.lib.rtb200_device_free(self._ctx, C.c_void_p(ptr)))
+
+    def ipc_export(self, ptr: int) -> bytes:
+        h = (C.c_uint8 * 64)()
+        _abi.check(_abi.lib.rtb200_ipc_export(self._ctx, C.c_void_p(ptr), h))
+        return bytes(h)
+
+    def ipc_open(self, handle: bytes) -> int:
+        h = (C.c_uint8 * 64)(*handle)
+        p = C.c_void_p()
+        _abi.check(_abi.lib.rtb200_ipc_open(self._ctx, h, C.byref(p)))
+        return int(p.value)
+
+    def ipc_close(self, ptr: int) -> None:
+        _abi.check(_abi.lib.rtb200_ipc_close(self._ctx, C.c_void_p(ptr)))
+
+    def resolve_peers_device(self, accum_ptrs, pixel_begin: int, pixel_end: int, samples_per_pixel: int, rgb8_ptr: int, stream: int = 0) -> None:
+        """Fused reduce (sum over accum_ptrs, in order) + resolve of pixels [pixel_begin, pixel_end) into the whole-image
+        RGB8 buffer at rgb8_ptr (local or peer)."""
+        arr = (C.c_void_p * len(accum_ptrs))(*[C.c_void_p(p) for p in accum_ptrs])
+        _abi.check(_abi.lib.rtb200_resolve_peers_device(self._ctx, arr, len(accum_ptrs), int(pixel_begin), int(pixel_end),
+                                                        int(samples_per_pixel), C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
+
     def read_counters(self) -> Tuple[int, int]:
         p, s = C.c_uint64(), C.c_uint64()
         _abi.check(_abi.lib.rtb200_read_counters(self._ctx, C.byref(p), C.byref(s)))

@@ -1,0 +1,80 @@
+"""Two ranks on two GPUs (NCCL): sample-range and row-range sharding with both framebuffer exchanges — the fused NVLink
+peer-memory reduce+resolve kernel (CUDA IPC) and the NCCL reduce baseline — against the single-GPU render of the
+whole job.  Skipped on a box with fewer than two GPUs (run with `gpurun --gpus 2`)."""
+import importlib
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+W, H, SPP, DEPTH, SEED = 322, 181, 12, 50, 4      # odd sizes: pixel slices that are not multiples of 4
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        rtb = importlib.import_module("rust-ray-tracing_b200")
+        dmod = importlib.import_module("rust-ray-tracing_b200.distributed")
+        scene = rtb.scenes.random_spheres()
+        cam = rtb.Camera.default(W, H)
+        r = rtb.CudaRenderer(device=rank, seed=SEED)
+        tracer = dmod.CudaTracer(r, scene)
+        out = {}
+        for mode in ("samples", "rows"):
+            for exchange in ("p2p", "nccl"):
+                sr = dmod.ShardedRenderer(tracer, mode=mode, exchange=exchange)
+                a = sr.render(DEPTH, SPP, cam)
+                b = sr.render(DEPTH, SPP, cam)
+                assert sr.exchange_in_use() == exchange
+                if rank == 0:
+                    assert np.array_equal(a, b)                  # deterministic
+                    out[(mode, exchange)] = a
+                else:
+                    assert a is None and b is None
+                if sr._peer is not None:
+                    sr._peer.close()
+        if rank == 0:
+            whole, _ = r.render(DEPTH, SPP, scene, cam)
+            q.put((out, whole))
+        dist.barrier()
+        r.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_exchanges_match_single_gpu():
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    out, whole = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    # rows: disjoint pixels, no summation -> identical; samples: two partial sums added -> float re-association only
+    for ex in ("p2p", "nccl"):
+        assert np.array_equal(out[("rows", ex)], whole)
+        d = np.abs(out[("samples", ex)].astype(int) - whole.astype(int))
+        assert d.max() <= 1 and (d > 0).mean() < 1e-3
+    assert np.array_equal(out[("samples", "p2p")], out[("samples", "nccl")]) or \
+        np.abs(out[("samples", "p2p")].astype(int) - out[("samples", "nccl")].astype(int)).max() <= 1
