@@ -241,9 +241,14 @@ class ShardedRenderer:
             return self.tracer.resolve(accum, spp_total)
         return None
 
-    def render(self, max_bounces: int, spp_total: int, camera):
-        """Host-facing call: returns the [H,W,3] uint8 numpy image on dst, None elsewhere."""
-        out = self.render_device(max_bounces, spp_total, camera)
-        if out is None:
+    def render(self, max_bounces: int, spp_total: int, camera, out=None):
+        """Host-facing call: returns the [H,W,3] uint8 numpy image on dst, None elsewhere.  `out`: optional host tensor
+        (e.g. torch.empty(..., pin_memory=True)) that receives the image instead of a fresh array."""
+        img = self.render_device(max_bounces, spp_total, camera)
+        if img is None:
             return None
-        return out.cpu().numpy()
+        if out is not None:
+            out.copy_(img, non_blocking=True)
+            self.tracer.torch.cuda.current_stream(self.tracer.device).synchronize()
+            return out.numpy()
+        return img.cpu().numpy()
