@@ -178,7 +178,7 @@ def run_ours(args):
     spp_total = spp_per_gpu * world            # weak scaling: per-GPU work fixed
     scene = getattr(rtb.scenes, gen)()
     cam = rtb.Camera.default(W, H)
-    renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays)
+    renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays, stages=args.stages)
     tracer = dmod.CudaTracer(renderer, scene)
     sharded = dmod.ShardedRenderer(tracer, mode="samples", exchange=args.exchange)
     info = renderer.device_info()
@@ -298,7 +298,7 @@ def run_ours(args):
                                                                    "nccl": "NCCL reduce(sum) to rank 0 + resolve"}[sharded.exchange_in_use()])
                        if world > 1 else "single GPU",
                        "l2": "no reuse across steps: each step re-traces from the camera; inputs are KBs, the framebuffer is written once",
-                       "seed": 1, "rays_per_lane": args.rays},
+                       "seed": 1, "rays_per_lane": args.rays, "stages": args.stages},
             "sphere_tests_per_s": tests_s, "segments_per_path": segs / max(paths, 1.0),
             "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": peak_tflops, "unit": "TFLOP/s",
                          "frac": achieved_tflops / peak_tflops, "traffic": traffic,
@@ -326,6 +326,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()

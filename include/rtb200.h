@@ -85,7 +85,9 @@ typedef struct rtb200_params {
 
 #define RTB200_FLAG_NONE 0
 #define RTB200_FLAG_RAYS1 1 /* force the one-ray-per-lane trace kernel  */
-#define RTB200_FLAG_RAYS2 2 /* force the two-rays-per-lane trace kernel */
+#define RTB200_FLAG_RAYS2 2 /* force the two-rays-per-lane (parameter-space) trace kernel */
+#define RTB200_FLAG_ONE_STAGE 4 /* parameter-space kernel: all pairs through the 8-instruction filter (no slab stage) */
+#define RTB200_FLAG_TWO_STAGE 8 /* parameter-space kernel: force the slab stage even where the scene layout does not favour it */
 
 /* Mirror of RenderStat (src/renderer.rs:11-34) plus the counters the metric needs. */
 typedef struct rtb200_stats {

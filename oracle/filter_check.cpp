@@ -23,6 +23,7 @@ struct Sph { float cx, cy, cz, r; };
 
 struct Tally {
     uint64_t pairs = 0, ref_pos = 0, flagged = 0, false_neg = 0;
+    uint64_t slab_flagged[3] = {0, 0, 0}, slab_false_neg = 0;   // stage 1 (slab test), per dropped axis
     double min_slack = 1e300;   // min over reference-positive pairs of q / (ray margin + sphere margin)
 };
 
@@ -59,8 +60,11 @@ static void worker(int scenario, uint64_t pairs, uint64_t seed, Tally* out) {
     std::uniform_real_distribution<double> U(0.0, 1.0);
     Tally t;
     std::vector<Sph> scene = make_scene(scenario, g);
-    std::vector<float> k(scene.size());
-    for (size_t i = 0; i < scene.size(); i++) k[i] = rtb::filter_sphere_k(scene[i].cx, scene[i].cy, scene[i].cz, scene[i].r * scene[i].r);
+    std::vector<float> k(scene.size()), rp(scene.size());
+    for (size_t i = 0; i < scene.size(); i++) {
+        k[i] = rtb::filter_sphere_k(scene[i].cx, scene[i].cy, scene[i].cz, scene[i].r * scene[i].r);
+        rp[i] = rtb::slab_sphere_r(scene[i].cx, scene[i].cy, scene[i].cz, scene[i].r * scene[i].r);
+    }
     const int n = (int)scene.size();
     while (t.pairs < pairs) {
         // --- origin
@@ -100,6 +104,8 @@ static void worker(int scenario, uint64_t pairs, uint64_t seed, Tally* out) {
         Ray<float> ray{{of[0], of[1], of[2]}, {(float)(d[0] * scale), (float)(d[1] * scale), (float)(d[2] * scale)}};
         float a = packed_length_squared(ray.d);
         rtb::FilterRay fr = rtb::make_filter_ray(ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, a);
+        rtb::SlabRay sr[3];
+        for (int up = 0; up < 3; up++) sr[up] = rtb::make_slab_ray(ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, a, up);
         double o2 = (double)of[0] * of[0] + (double)of[1] * of[1] + (double)of[2] * of[2];
         // --- the aimed-at sphere plus a handful of others per ray
         for (int rep = 0; rep < 8 && t.pairs < pairs; rep++) {
@@ -115,6 +121,13 @@ static void worker(int scenario, uint64_t pairs, uint64_t seed, Tally* out) {
             t.ref_pos += ref;
             t.flagged += flag;
             if (ref && !flag) t.false_neg++;
+            for (int up = 0; up < 3; up++) {
+                const float cc[3] = {sp.cx, sp.cy, sp.cz};
+                const int ia = (up + 1) % 3, ib = (up + 2) % 3;
+                bool sflag = !std::signbit(rtb::slab_value(sr[up], cc[ia], cc[ib], rp[si]));
+                t.slab_flagged[up] += sflag;
+                if (ref && !sflag) t.slab_false_neg++;
+            }
             if (ref) {
                 double b = std::sqrt((double)sp.cx * sp.cx + (double)sp.cy * sp.cy + (double)sp.cz * sp.cz) + sp.r;
                 double margin = (double)RTB_FILTER_MARGIN * (o2 + b * b);
@@ -138,10 +151,14 @@ int main(int argc, char** argv) {
     Tally t;
     for (auto& x : tl) {
         t.pairs += x.pairs; t.ref_pos += x.ref_pos; t.flagged += x.flagged; t.false_neg += x.false_neg;
+        for (int up = 0; up < 3; up++) t.slab_flagged[up] += x.slab_flagged[up];
+        t.slab_false_neg += x.slab_false_neg;
         t.min_slack = std::min(t.min_slack, x.min_slack);
     }
     std::printf("{\"scenario\": %d, \"pairs\": %" PRIu64 ", \"ref_positive\": %" PRIu64 ", \"flagged\": %" PRIu64
-                ", \"false_negatives\": %" PRIu64 ", \"min_slack\": %.6g}\n",
-                scenario, t.pairs, t.ref_pos, t.flagged, t.false_neg, t.min_slack);
-    return t.false_neg == 0 ? 0 : 1;
+                ", \"false_negatives\": %" PRIu64 ", \"min_slack\": %.6g, \"slab_flagged\": [%" PRIu64 ", %" PRIu64 ", %" PRIu64
+                "], \"slab_false_negatives\": %" PRIu64 "}\n",
+                scenario, t.pairs, t.ref_pos, t.flagged, t.false_neg, t.min_slack, t.slab_flagged[0], t.slab_flagged[1], t.slab_flagged[2],
+                t.slab_false_neg);
+    return (t.false_neg == 0 && t.slab_false_neg == 0) ? 0 : 1;
 }

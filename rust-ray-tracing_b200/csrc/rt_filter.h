@@ -94,4 +94,66 @@ inline float filter_sphere_k(float cx, float cy, float cz, float r2) {
     return nextafterf(kf, -INFINITY);
 }
 
+// ---- stage 1 of the two-stage sweep: the slab test ------------------------------------------------------------------
+// A cheaper conservative test that runs for ALL pairs in the parameter-space kernel; its candidates (a few per cent
+// of the pairs) then go through filter_value above and, if they pass that too, through the exact arithmetic.
+//
+// Drop one coordinate axis (`up`, chosen per scene by the host: the axis along which the sphere centres spread least)
+// and look at the scene from along it: the ray becomes a line in the remaining (a, b) plane, and a sphere the line of
+// sight misses by more than its radius cannot be hit.  With U = (d_b, -d_a)/|(d_a, d_b)| (a unit vector orthogonal to
+// the ray, with no `up` component)
+//     p = (c_a - o_a) U_a + (c_b - o_b) U_b          2 FFMA   (per ray: U_a, U_b, -(o.U))
+//     q = R' - p^2 + M_r                             FFMA + FADD, candidate <=> sign bit clear
+// |p| is the length of a projection of the centre-to-line vector, so |p| <= dist(c, line); the reference's computed
+// discriminant is >= 0 only if dist^2 <= r^2 + 24u(|OC|^2 + r^2), and p carries a rounding error of at most 16u*S
+// (S = |o| + |c| + r): (dist + 16uS)^2 <= r^2 + 96u*S^2 again, split as for the filter into the sphere's half
+// R' = r^2 + 192u(|c|+r)^2 (host, f64, rounded up) and the ray's half M_r = 192u|o|^2.
+struct SlabRay {
+    float ua, ub, nou, mr;
+};
+
+// Component `axis` of a vector given as three scalars (axis is warp-uniform).
+RTB_HD float axis_pick(float x, float y, float z, int axis) { return axis == 0 ? x : axis == 1 ? y : z; }
+
+// up = the dropped axis (0, 1, 2); a = (up + 1) % 3, b = (up + 2) % 3.  a2 = d.d as the sweep computes it.
+RTB_HD SlabRay make_slab_ray(float ox, float oy, float oz, float dx, float dy, float dz, float a2, int up) {
+    SlabRay s;
+    const int ia = up == 2 ? 0 : up + 1, ib = ia == 2 ? 0 : ia + 1;
+    float o2 = RTB_FMA(oz, oz, RTB_FMA(oy, oy, RTB_MUL(ox, ox)));
+    if (!(a2 >= 1e-30f && a2 <= 1e30f && o2 <= 1e30f)) {     // degenerate ray: everything is a candidate (q = R' + 3e38)
+        s.ua = s.ub = s.nou = 0.0f;
+        s.mr = 3.0e38f;
+        return s;
+    }
+    float inv_len = RTB_RSQRT(a2);
+    float ha = RTB_MUL(axis_pick(dx, dy, dz, ia), inv_len), hb = RTB_MUL(axis_pick(dx, dy, dz, ib), inv_len);
+    float h2 = RTB_FMA(hb, hb, RTB_MUL(ha, ha));
+    if (h2 < 1e-15f) {                                        // ray along `up`: any direction in the (a, b) plane is orthogonal
+        s.ua = 1.0f; s.ub = 0.0f;
+    } else {
+        float inv = RTB_RSQRT(h2);
+        s.ua = RTB_MUL(hb, inv); s.ub = -RTB_MUL(ha, inv);
+    }
+    float oa = axis_pick(ox, oy, oz, ia), ob = axis_pick(ox, oy, oz, ib);
+    s.nou = -RTB_FMA(ob, s.ub, RTB_MUL(oa, s.ua));
+    s.mr = RTB_MUL(RTB_FILTER_MARGIN, o2);
+    return s;
+}
+
+// 4 FP32 instructions per (ray, sphere): sign bit clear <=> candidate.  Sphere = {c_a, c_b, R'}.
+RTB_HD float slab_value(const SlabRay& s, float ca, float cb, float rp) {
+    float p = RTB_FMA(ca, s.ua, RTB_FMA(cb, s.ub, s.nou));
+    return RTB_ADD(RTB_FMA(-p, p, rp), s.mr);
+}
+
+// Per-sphere half of the slab test, f64 on the host from the DEVICE values: R' = r^2 + 192u(|c| + r)^2, rounded to float
+// and stepped one ulp up.
+inline float slab_sphere_r(float cx, float cy, float cz, float r2) {
+    double c2 = (double)cx * cx + (double)cy * cy + (double)cz * cz;
+    double r = sqrt(r2 > 0.0f ? (double)r2 : 0.0);
+    double b = sqrt(c2) + r;
+    double rp = (double)(r2 > 0.0f ? r2 : 0.0f) + (double)RTB_FILTER_MARGIN * b * b;
+    return nextafterf((float)rp, INFINITY);
+}
+
 }  // namespace rtb

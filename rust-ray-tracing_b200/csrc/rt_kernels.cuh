@@ -292,6 +292,94 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
     }
 }
 
+// Stages 2 and 3 of the two-stage sweep for ONE ray and one chunk of up to 8 blocks: a lane-parallel walk over the
+// stage-1 candidates in sweep order.  `todo` has one bit per block of the chunk that holds a candidate (bit b = block b);
+// the block counter is derived from it, so it is a genuinely per-lane value.  (Written with a plain counter that only
+// ever takes warp-uniform VALUES, at lane-dependent TIMES, ptxas 12.9 parked it in a uniform register which partial
+// warps then advanced: lanes skipped blocks.)  One out-of-line copy serves both rays of the lane (instruction cache).
+struct Best { float t; int i; };
+
+__device__ __noinline__ Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere, int count,
+                                          const float4* __restrict__ g_filter, const float4* __restrict__ g_exact, FilterRay f, ExactRay ray,
+                                          Best best) {
+    if (todo == 0u) return best;
+    const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                          // src/objects.rs:253
+    const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
+    uint32_t cand = 0;
+    int base = 0;
+    for (;;) {
+        if (cand == 0u) {
+            if (todo == 0u) break;
+            const int b = __ffs(todo) - 1;
+            todo &= todo - 1u;
+            cand = ~masks_r[b * stride];                   // not empty: stage 1 set the block's bit
+            base = first_sphere + b * SWEEP_BLOCK;
+        }
+        const int j = __clz(cand);
+        cand &= ~(0x80000000u >> j);
+        const int idx = base + j;
+        if (idx < count) {                                 // padding of the last block is never tested
+            const float4 fs = __ldg(&g_filter[idx]);
+            const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                               // stage 2
+            if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&g_exact[idx]), idx, best.t, best.i);   // stage 3
+        }
+    }
+    return best;
+}
+
+// The two-stage sweep of the parameter-space kernel.
+//   stage 1, all pairs, uniform control flow: the slab test (rt_filter.h: 2 FFMA + FFMA + FADD, sphere operands in uniform
+//            registers, one funnel shift per pair) -> one 32-bit mask per 32-sphere block and ray, stored unconditionally
+//            (8 words per ray: the scene is swept in chunks of 8 blocks = 256 spheres), and a per-ray bit per block
+//            that holds a candidate;
+//   stage 2, lane-parallel over the stage-1 candidates of the chunk (a few per cent of the pairs), in sweep order: the
+//            8-instruction filter (filter_value), and for those that pass it
+//   stage 3, the reference's exact arithmetic (test_candidate).
+// Both filters are conservative, so the result equals the reference's sequential `update` over the object list.
+// masks layout: word b of ray r of this thread at masks[(r * 8 + b) * stride].
+template <int RAYS, class PV_T, class RaySrc>
+__device__ __forceinline__ void sweep_two_stage(const PV_T& pv, const RaySrc& rays, const float4* __restrict__ g_filter,
+                                                const float4* __restrict__ g_exact, int count, uint32_t* masks, int stride,
+                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+    const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the parameter array is padded to whole blocks
+    for (int cb = 0; cb < n_blocks; cb += 8) {
+        const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
+        uint32_t todo[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) todo[r] = 0u;
+        // ---- stage 1 ----
+        uint32_t bit = 1u;
+#pragma unroll 1
+        for (int b = 0; b < nb; b++, bit <<= 1) {
+            uint32_t mask[RAYS];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = 0;
+            const int pair0 = (cb + b) * (SWEEP_BLOCK / 2);
+#pragma unroll
+            for (int j = 0; j < SWEEP_BLOCK / 2; j++) {
+                const float2 A = pv.s1[3 * (pair0 + j)], B = pv.s1[3 * (pair0 + j) + 1], C = pv.s1[3 * (pair0 + j) + 2];
+#pragma unroll
+                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, B.x)), mask[r], 1);
+#pragma unroll
+                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.y, C.x, C.y)), mask[r], 1);
+            }
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                masks[(r * 8 + b) * stride] = mask[r];
+                todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
+            }
+        }
+        // ---- stages 2 and 3 ----
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            Best bst{best_t[r], best_i[r]};
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, count, g_filter, g_exact, f[r], rays.load(r), bst);
+            best_t[r] = bst.t;
+            best_i[r] = bst.i;
+        }
+    }
+}
+
 // ---- K1 ----------------------------------------------------------------------------------------------------------
 // One thread per ray; spheres streamed through shared memory in tiles of `tile` (multiple of SWEEP_BLOCK).
 // dynamic smem: tile float4 + LIST_CAP * blockDim uint2.
@@ -349,8 +437,23 @@ struct TraceParams {
 // N spheres: the sweep then takes its sphere operand from uniform registers (ParamSpheres).
 template <int N>
 struct TraceParamsV {
+    static constexpr bool two_stage = false;
+    static constexpr int capacity = N;
     TraceParams b;
     float4 flt[N];
+};
+
+// TraceParams + the STAGE-1 (slab test, rt_filter.h) spheres in parameter space: three floats {c_a, c_b, R'} per sphere
+// with the scene's `up` axis dropped, two spheres per three float2 (LDCU.64 x3 per pair), padded to a multiple of 32
+// spheres with never-candidates (R' = -inf).  Up to N spheres (N = 2560: 30 KB of parameters).
+template <int N>
+struct TraceParamsS {
+    static constexpr bool two_stage = true;
+    static constexpr int capacity = N;
+    TraceParams b;
+    int up_axis;
+    int _pad[3];
+    float2 s1[N * 3 / 2];
 };
 
 template <int N>
@@ -576,8 +679,8 @@ struct SmemRays {
     }
 };
 
-template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, int N>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __grid_constant__ TraceParamsV<N> PV) {
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, class PV_T>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __grid_constant__ PV_T PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
     uint32_t* st = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
@@ -632,8 +735,17 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             best_t[r] = RTB_INF;
             best_i[r] = -1;
         }
-        sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<N>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS, flt, best_t,
-                                        best_i);
+        if constexpr (PV_T::two_stage) {
+            static_assert(CAP >= 8, "the two-stage sweep keeps 8 mask words per ray");
+            SlabRay slab[RAYS];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++)
+                slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis);
+            sweep_two_stage<RAYS>(PV, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+        } else {
+            sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS,
+                                            flt, best_t, best_i);
+        }
 #pragma unroll
         for (int r = 0; r < RAYS; r++) { W(15, r) = __float_as_uint(best_t[r]); W(16, r) = (uint32_t)best_i[r]; }
         swept = true;

@@ -4,6 +4,7 @@
 #include "../../include/rtb200.h"
 #include "rt_kernels.cuh"
 
+#include <algorithm>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -45,7 +46,10 @@ struct rtb200_ctx {
     float4* d_spheres = nullptr;
     float4* d_filter = nullptr;
     std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
-    std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsV<1024>) + 64);
+    std::vector<float> h_slab;                         // stage-1 spheres {c_a, c_b, R'} padded to whole 32-blocks (two-stage variant)
+    int up_axis = 1;                                   // the axis the slab test drops
+    double slab_pass = 1.0;                            // estimated fraction of pairs that pass stage 1
+    std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsS<2560>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
     int n_spheres = 0;
@@ -151,13 +155,21 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     //   m1 : resident kernel, 256 threads x 4 CTAs/SM, spheres staged in shared memory (up to ~2 000 spheres).
     //   l1 : resident kernel, 1024 threads x 1 CTA/SM (up to ~11 000 spheres).
     constexpr int CG = rtb::LIST_CAP, CV = rtb::LIST_CAP_V, VT = 256, VR = 2;
-    auto k_v512 = rtb::k_trace_paths_v<VT, 4, VR, CV, 512>;
-    auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, 1024>;
+    using PV512 = rtb::TraceParamsV<512>;
+    using PV1024 = rtb::TraceParamsV<1024>;
+    using PS512 = rtb::TraceParamsS<512>;
+    using PS2560 = rtb::TraceParamsS<2560>;
+    auto k_v512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV512>;
+    auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV1024>;
+    auto k_s512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS512>;
+    auto k_s2560 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS2560>;
     auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
     auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
     if (!ctx->attrs_set) {
         CU_TRY(cudaFuncSetAttribute(k_v512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_v1024, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_s512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_s2560, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
@@ -168,14 +180,32 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const size_t smem_m1 = trace_smem_bytes(P.n_spheres, SMALL_THREADS, 1, CG);
     const size_t smem_l1 = trace_smem_bytes(P.n_spheres, LARGE_THREADS, 1, CG);
     int want = (p->flags & RTB200_FLAG_RAYS2) ? 2 : (p->flags & RTB200_FLAG_RAYS1) ? 1 : ctx->default_rays;
-    const bool use_v = want != 1 && P.n_spheres <= 1024 && (smem_v + 1024) * 4 <= per_sm;
-    if (use_v && P.n_spheres <= 512) {
-        auto* pv = reinterpret_cast<rtb::TraceParamsV<512>*>(ctx->h_params.data());
+    const bool fits_v = want != 1 && (smem_v + 1024) * 4 <= per_sm;
+    // two-stage (slab test first) when the scene's layout lets stage 1 reject most pairs; RTB200_FLAG_ONE_STAGE forces
+    // the single-stage parameter-space kernel, RTB200_FLAG_TWO_STAGE the two-stage one.
+    const bool two_stage = fits_v && P.n_spheres <= 2560 && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
+                           ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
+    const bool use_v = fits_v && !two_stage && P.n_spheres <= 1024;
+    auto fill_s = [&](auto* ps) {
+        ps->b = P;
+        ps->up_axis = ctx->up_axis;
+        std::memcpy(ps->s1, ctx->h_slab.data(), ctx->h_slab.size() * sizeof(float));
+    };
+    if (two_stage && P.n_spheres <= 512) {
+        auto* ps = reinterpret_cast<PS512*>(ctx->h_params.data());
+        fill_s(ps);
+        k_s512<<<sms * 4, VT, smem_v, st>>>(*ps);
+    } else if (two_stage) {
+        auto* ps = reinterpret_cast<PS2560*>(ctx->h_params.data());
+        fill_s(ps);
+        k_s2560<<<sms * 4, VT, smem_v, st>>>(*ps);
+    } else if (use_v && P.n_spheres <= 512) {
+        auto* pv = reinterpret_cast<PV512*>(ctx->h_params.data());
         pv->b = P;
         std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
         k_v512<<<sms * 4, VT, smem_v, st>>>(*pv);
     } else if (use_v) {
-        auto* pv = reinterpret_cast<rtb::TraceParamsV<1024>*>(ctx->h_params.data());
+        auto* pv = reinterpret_cast<PV1024*>(ctx->h_params.data());
         pv->b = P;
         std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
         k_v1024<<<sms * 4, VT, smem_v, st>>>(*pv);
@@ -372,6 +402,38 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);
+    {   // stage-1 data of the two-stage sweep: drop the axis along which the centres spread least (robust spread: the
+        // 10%..90% range, so that one huge "ground" sphere does not decide), estimate how many pairs will pass
+        int up = 1;
+        double spread[3] = {0, 0, 0};
+        if (n > 0) {
+            std::vector<float> v((size_t)n);
+            for (int ax = 0; ax < 3; ax++) {
+                for (int i = 0; i < n; i++) v[i] = ax == 0 ? sph[i].x : ax == 1 ? sph[i].y : sph[i].z;
+                std::sort(v.begin(), v.end());
+                spread[ax] = (double)v[(size_t)((n - 1) * 0.9)] - (double)v[(size_t)((n - 1) * 0.1)];
+            }
+            up = spread[0] <= spread[1] && spread[0] <= spread[2] ? 0 : (spread[1] <= spread[2] ? 1 : 2);
+        }
+        const int ia = (up + 1) % 3, ib = (up + 2) % 3;
+        const int padded = (n + 31) / 32 * 32;
+        ctx->h_slab.assign((size_t)padded * 3, 0.0f);
+        const double extent = std::max(1e-30, 0.5 * (spread[ia] + spread[ib]));
+        double pass = 0.0;
+        for (int i = 0; i < padded; i++) {
+            float* o3 = &ctx->h_slab[(size_t)i * 3];
+            if (i < n) {
+                const float c[3] = {sph[i].x, sph[i].y, sph[i].z};
+                o3[0] = c[ia]; o3[1] = c[ib];
+                o3[2] = rtb::slab_sphere_r(sph[i].x, sph[i].y, sph[i].z, sph[i].w);
+                pass += std::min(1.0, 2.0 * std::sqrt((double)o3[2]) / extent);
+            } else {
+                o3[2] = -INFINITY;                        // padding: never a candidate
+            }
+        }
+        ctx->up_axis = up;
+        ctx->slab_pass = n > 0 ? pass / n : 1.0;
+    }
     return RTB200_OK;
 }
 

@@ -104,12 +104,17 @@ def _render_both(rtb, renderer, oracle, scene, W, H, spp, depth, seed=1, camera=
     return img, lin, stat, ref_sum, ref_rgb, ref_seg
 
 
-@pytest.mark.parametrize("rays", [1, 2])
+# kernel variants: (rays_per_lane, stages) — resident one-ray kernel, parameter-space one-stage, parameter-space two-stage
+VARIANTS = [(1, 0), (2, 1), (2, 2)]
+
+
+@pytest.mark.parametrize("rays,stages", VARIANTS)
 @pytest.mark.parametrize("scene_name,W,H,spp", [("three_spheres", 400, 225, 16), ("random_spheres", 192, 108, 8),
                                                  ("dielectric_heavy", 160, 90, 8)])
-def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp, rays):
+def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp, rays, stages):
     scene = getattr(rtb.scenes, scene_name)()
     renderer.rays_per_lane = rays
+    renderer.stages = stages
     img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
     mean = lin[..., :3].astype(np.float64) / spp
     err = np.abs(mean - ref_sum / spp).max()
@@ -120,18 +125,21 @@ def test_render_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp, ray
     assert np.array_equal(img, ref_rgb)                  # quantised image identical
     assert np.all(lin[..., 3] == spp)
     renderer.rays_per_lane = 0
+    renderer.stages = 0
 
 
-@pytest.mark.parametrize("rays", [1, 2])
-def test_render_depth_limit_and_seed(rtb, renderer, oracle, rays):
+@pytest.mark.parametrize("rays,stages", VARIANTS)
+def test_render_depth_limit_and_seed(rtb, renderer, oracle, rays, stages):
     scene = rtb.scenes.three_spheres()
     renderer.rays_per_lane = rays
+    renderer.stages = stages
     for depth, seed in ((1, 1), (2, 1), (5, 77), (0, 1)):
         img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 80, 45, 4, depth, seed=seed)
         assert np.abs(lin[..., :3] / 4.0 - ref_sum / 4.0).max() <= 1e-4
         assert stat.segments == ref_seg
         assert np.array_equal(img, ref_rgb)
     renderer.rays_per_lane = 0
+    renderer.stages = 0
 
 
 def test_render_defocus_camera(rtb, renderer, oracle):
@@ -236,16 +244,18 @@ def test_candidate_list_overflow_intersect(rtb, renderer, oracle, n):
     assert (idx[: m // 2] >= 0).mean() > 0.9 and np.all(idx[m // 2:] == -1)
 
 
-@pytest.mark.parametrize("rays", [1, 2])
+@pytest.mark.parametrize("rays,stages", VARIANTS)
 @pytest.mark.parametrize("n", [486, 700, 1500])
-def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays):
+def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays, stages):
     """Renders through every trace-kernel variant (parameter-space <= 512 / <= 1024 spheres, resident beyond) with rays
     that carry far more candidate blocks than the per-ray lists hold."""
     scene = _tube_scene(rtb, n)
     cam = rtb.Camera(96, 54, 1.0, 40.0, (0.3, 0.2, 2.0), (0.0, 0.0, -10.0), (0.0, 1.0, 0.0), 0.0)
     renderer.rays_per_lane = rays
+    renderer.stages = stages
     img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 96, 54, 4, 12, camera=cam)
     renderer.rays_per_lane = 0
+    renderer.stages = 0
     assert np.abs(lin[..., :3].astype(np.float64) / 4 - ref_sum / 4).max() <= 1e-4
     assert stat.segments == ref_seg
     assert np.array_equal(img, ref_rgb)
