@@ -296,10 +296,14 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
 // stage-1 candidates in sweep order.  `todo` has one bit per block of the chunk that holds a candidate (bit b = block b);
 // the block counter is derived from it, so it is a genuinely per-lane value.  (Written with a plain counter that only
 // ever takes warp-uniform VALUES, at lane-dependent TIMES, ptxas 12.9 parked it in a uniform register which partial
-// warps then advanced: lanes skipped blocks.)  One out-of-line copy serves both rays of the lane (instruction cache).
+// warps then advanced: lanes skipped blocks.)  The device arrays are padded to whole blocks with never-hit spheres, so
+// a padding bit that slips through stage 1 (NaN ray) is harmless.
 struct Best { float t; int i; };
+#ifndef RTB_REFINE_INLINE
+#define RTB_REFINE_INLINE __forceinline__   // two inlined copies (one per ray of the lane) beat one out-of-line copy by 5 %
+#endif
 
-__device__ __noinline__ Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere, int count,
+__device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
                                           const float4* __restrict__ g_filter, const float4* __restrict__ g_exact, FilterRay f, ExactRay ray,
                                           Best best) {
     if (todo == 0u) return best;
@@ -318,11 +322,9 @@ __device__ __noinline__ Best refine_chunk(const uint32_t* masks_r, int stride, u
         const int j = __clz(cand);
         cand &= ~(0x80000000u >> j);
         const int idx = base + j;
-        if (idx < count) {                                 // padding of the last block is never tested
-            const float4 fs = __ldg(&g_filter[idx]);
-            const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                               // stage 2
-            if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&g_exact[idx]), idx, best.t, best.i);   // stage 3
-        }
+        const float4 fs = __ldg(&g_filter[idx]);
+        const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2
+        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&g_exact[idx]), idx, best.t, best.i);   // stage 3
     }
     return best;
 }
@@ -373,7 +375,7 @@ __device__ __forceinline__ void sweep_two_stage(const PV_T& pv, const RaySrc& ra
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, count, g_filter, g_exact, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }

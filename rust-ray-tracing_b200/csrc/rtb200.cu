@@ -358,8 +358,12 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     if (scene->n_spheres < 0 || scene->n_materials < 0) return fail(RTB200_ERR_INVALID, "negative count");
     if (scene->n_spheres > 0 && (!scene->spheres || !scene->materials)) return fail(RTB200_ERR_INVALID, "null scene arrays");
     const int n = scene->n_spheres;
-    std::vector<float4> sph((size_t)(n > 0 ? n : 1)), flt((size_t)(n > 0 ? n : 1)), mat((size_t)(n > 0 ? n : 1));
-    std::vector<int> kind((size_t)(n > 0 ? n : 1));
+    // device arrays are padded to whole 32-sphere blocks with spheres that can never be hit: exact {0,0,0,r^2 = -1}
+    // (discriminant < 0 for every ray), filter {0,0,0,k = +inf} (never a candidate)
+    const size_t cnt = (size_t)((n + 31) / 32 * 32 > 0 ? (n + 31) / 32 * 32 : 32);
+    std::vector<float4> sph(cnt, make_float4(0.f, 0.f, 0.f, -1.0f)), flt(cnt, make_float4(0.f, 0.f, 0.f, INFINITY)),
+        mat(cnt, make_float4(0.f, 0.f, 0.f, 0.f));
+    std::vector<int> kind(cnt, 0);
     for (int i = 0; i < n; i++) {
         const rtb200_sphere& s = scene->spheres[i];
         if (s.material < 0 || s.material >= scene->n_materials)
@@ -380,7 +384,6 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     }
     CU_TRY(cudaSetDevice(ctx->device));
     // One device arena [spheres | filter | materials | kinds], reused while it is large enough, filled by ONE copy.
-    const size_t cnt = (size_t)(n > 0 ? n : 1);
     const size_t bytes = cnt * (3 * sizeof(float4) + sizeof(int));
     if (ctx->scene_capacity < bytes) {
         cudaFree(ctx->d_scene);
