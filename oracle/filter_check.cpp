@@ -66,6 +66,7 @@ static void worker(int scenario, uint64_t pairs, uint64_t seed, Tally* out) {
         rp[i] = rtb::slab_sphere_r(scene[i].cx, scene[i].cy, scene[i].cz, scene[i].r * scene[i].r);
     }
     const int n = (int)scene.size();
+    const float rp_min = rtb::slab_apply_floor(rp.data(), n, 1);   // as rtb200_upload_scene does
     while (t.pairs < pairs) {
         // --- origin
         double o[3];
@@ -105,7 +106,7 @@ static void worker(int scenario, uint64_t pairs, uint64_t seed, Tally* out) {
         float a = packed_length_squared(ray.d);
         rtb::FilterRay fr = rtb::make_filter_ray(ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, a);
         rtb::SlabRay sr[3];
-        for (int up = 0; up < 3; up++) sr[up] = rtb::make_slab_ray(ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, a, up);
+        for (int up = 0; up < 3; up++) sr[up] = rtb::make_slab_ray(ray.o.x, ray.o.y, ray.o.z, ray.d.x, ray.d.y, ray.d.z, a, up, rp_min);
         double o2 = (double)of[0] * of[0] + (double)of[1] * of[1] + (double)of[2] * of[2];
         // --- the aimed-at sphere plus a handful of others per ray
         for (int rep = 0; rep < 8 && t.pairs < pairs; rep++) {

@@ -330,7 +330,7 @@ __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stri
 }
 
 // The two-stage sweep of the parameter-space kernel.
-//   stage 1, all pairs, uniform control flow: the slab test (rt_filter.h: 2 FFMA + FFMA + FADD, sphere operands in uniform
+//   stage 1, all pairs, uniform control flow: the slab test (rt_filter.h: 3 FFMA, sphere operands in uniform
 //            registers, one funnel shift per pair) -> one 32-bit mask per 32-sphere block and ray, stored unconditionally
 //            (8 words per ray: the scene is swept in chunks of 8 blocks = 256 spheres), and a per-ray bit per block
 //            that holds a candidate;
@@ -454,7 +454,8 @@ struct TraceParamsS {
     static constexpr int capacity = N;
     TraceParams b;
     int up_axis;
-    int _pad[3];
+    float rp_min;                 // the scene's smallest (floored) R', make_slab_ray's scale
+    int _pad[2];
     float2 s1[N * 3 / 2];
 };
 
@@ -742,7 +743,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             SlabRay slab[RAYS];
 #pragma unroll
             for (int r = 0; r < RAYS; r++)
-                slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis);
+                slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             sweep_two_stage<RAYS>(PV, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
         } else {
             sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS,

@@ -48,6 +48,7 @@ struct rtb200_ctx {
     std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
     std::vector<float> h_slab;                         // stage-1 spheres {c_a, c_b, R'} padded to whole 32-blocks (two-stage variant)
     int up_axis = 1;                                   // the axis the slab test drops
+    float slab_rp_min = 1.0f;                          // smallest floored R' of the scene (rt_filter.h make_slab_ray)
     double slab_pass = 1.0;                            // estimated fraction of pairs that pass stage 1
     std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsS<2560>) + 64);
     float4* d_mat = nullptr;
@@ -189,6 +190,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto fill_s = [&](auto* ps) {
         ps->b = P;
         ps->up_axis = ctx->up_axis;
+        ps->rp_min = ctx->slab_rp_min;
         std::memcpy(ps->s1, ctx->h_slab.data(), ctx->h_slab.size() * sizeof(float));
     };
     if (two_stage && P.n_spheres <= 512) {
@@ -422,18 +424,22 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         const int padded = (n + 31) / 32 * 32;
         ctx->h_slab.assign((size_t)padded * 3, 0.0f);
         const double extent = std::max(1e-30, 0.5 * (spread[ia] + spread[ib]));
-        double pass = 0.0;
         for (int i = 0; i < padded; i++) {
             float* o3 = &ctx->h_slab[(size_t)i * 3];
             if (i < n) {
                 const float c[3] = {sph[i].x, sph[i].y, sph[i].z};
                 o3[0] = c[ia]; o3[1] = c[ib];
                 o3[2] = rtb::slab_sphere_r(sph[i].x, sph[i].y, sph[i].z, sph[i].w);
-                pass += std::min(1.0, 2.0 * std::sqrt((double)o3[2]) / extent);
             } else {
                 o3[2] = -INFINITY;                        // padding: never a candidate
             }
         }
+        ctx->slab_rp_min = rtb::slab_apply_floor(ctx->h_slab.data() + 2, n, 3);
+        // expected pass rate of stage 1: disc diameter over the scene's extent, inflated as for a ray that starts one
+        // extent away from the origin (the 1 + M_r/R_min of make_slab_ray)
+        const double inflate = 1.0 + (double)RTB_FILTER_MARGIN * extent * extent / (double)ctx->slab_rp_min;
+        double pass = 0.0;
+        for (int i = 0; i < n; i++) pass += std::min(1.0, 2.0 * std::sqrt((double)ctx->h_slab[(size_t)i * 3 + 2] * inflate) / extent);
         ctx->up_axis = up;
         ctx->slab_pass = n > 0 ? pass / n : 1.0;
     }
