@@ -339,11 +339,52 @@ __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stri
 //   stage 3, the reference's exact arithmetic (test_candidate).
 // Both filters are conservative, so the result equals the reference's sequential `update` over the object list.
 // masks layout: word b of ray r of this thread at masks[(r * 8 + b) * stride].
-template <int RAYS, class PV_T, class RaySrc>
-__device__ __forceinline__ void sweep_two_stage(const PV_T& pv, const RaySrc& rays, const float4* __restrict__ g_filter,
+// Stage-1 operand sources: evaluate the slab test of one 32-sphere block for the RAYS rays of a lane.
+// ParamSlab: {c_a, c_b, R'} triples in kernel parameter space -> LDCU.64 x3 per sphere pair, uniform-register operands.
+template <class PV_T>
+struct ParamSlab {
+    const PV_T& pv;
+    template <int RAYS>
+    __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
+        const int pair0 = blk * (SWEEP_BLOCK / 2);
+#pragma unroll
+        for (int j = 0; j < SWEEP_BLOCK / 2; j++) {
+            const float2 A = pv.s1[3 * (pair0 + j)], B = pv.s1[3 * (pair0 + j) + 1], C = pv.s1[3 * (pair0 + j) + 2];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, B.x)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.y, C.x, C.y)), mask[r], 1);
+        }
+    }
+};
+
+// SmemSlab: the same triples staged in shared memory (scenes too large for parameter space): three LDS.128 broadcasts
+// per four spheres, each serving the RAYS rays of the lane.
+struct SmemSlab {
+    const float4* s;
+    template <int RAYS>
+    __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
+        const float4* q = s + blk * (SWEEP_BLOCK / 4 * 3);
+#pragma unroll
+        for (int j = 0; j < SWEEP_BLOCK / 4; j++) {
+            const float4 A = q[3 * j], B = q[3 * j + 1], C = q[3 * j + 2];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, A.z)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.w, B.x, B.y)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.z, B.w, C.x)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], C.y, C.z, C.w)), mask[r], 1);
+        }
+    }
+};
+
+template <int RAYS, class S1, class RaySrc>
+__device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const float4* __restrict__ g_filter,
                                                 const float4* __restrict__ g_exact, int count, uint32_t* masks, int stride,
                                                 const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
-    const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the parameter array is padded to whole blocks
+    const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
         const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
         uint32_t todo[RAYS];
@@ -356,15 +397,7 @@ __device__ __forceinline__ void sweep_two_stage(const PV_T& pv, const RaySrc& ra
             uint32_t mask[RAYS];
 #pragma unroll
             for (int r = 0; r < RAYS; r++) mask[r] = 0;
-            const int pair0 = (cb + b) * (SWEEP_BLOCK / 2);
-#pragma unroll
-            for (int j = 0; j < SWEEP_BLOCK / 2; j++) {
-                const float2 A = pv.s1[3 * (pair0 + j)], B = pv.s1[3 * (pair0 + j) + 1], C = pv.s1[3 * (pair0 + j) + 2];
-#pragma unroll
-                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, B.x)), mask[r], 1);
-#pragma unroll
-                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.y, C.x, C.y)), mask[r], 1);
-            }
+            s1.template block<RAYS>(cb + b, sl, mask);
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
                 masks[(r * 8 + b) * stride] = mask[r];
@@ -451,12 +484,27 @@ struct TraceParamsV {
 template <int N>
 struct TraceParamsS {
     static constexpr bool two_stage = true;
+    static constexpr bool s1_smem = false;
     static constexpr int capacity = N;
     TraceParams b;
     int up_axis;
     float rp_min;                 // the scene's smallest (floored) R', make_slab_ray's scale
     int _pad[2];
     float2 s1[N * 3 / 2];
+};
+
+// TraceParams + a pointer to the stage-1 triples in global memory: the kernel stages them in SHARED memory (scenes of
+// more than 2560 spheres, up to what fits beside the path state: ~10 600 spheres).
+struct TraceParamsL {
+    static constexpr bool two_stage = true;
+    static constexpr bool s1_smem = true;
+    static constexpr int capacity = 1 << 30;
+    TraceParams b;
+    int up_axis;
+    float rp_min;
+    int n_padded;                 // spheres rounded up to whole 32-blocks
+    int _pad;
+    const float4* s1;             // n_padded * 3 floats, 16-byte aligned
 };
 
 template <int N>
@@ -690,6 +738,15 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
     uint32_t* list = reinterpret_cast<uint32_t*>(smem4) + SLOT_WORDS * RAYS * THREADS + threadIdx.x;
     auto W = [&](int w, int r) -> uint32_t& { return st[(w * RAYS + r) * THREADS]; };
     auto F = [&](int w, int r) -> float { return __uint_as_float(st[(w * RAYS + r) * THREADS]); };
+    [[maybe_unused]] const float4* s_slab = smem4 + (SLOT_WORDS + CAP) * RAYS * THREADS / 4;
+    if constexpr (PV_T::two_stage) {
+        if constexpr (PV_T::s1_smem) {                         // stage the stage-1 triples once per CTA
+            float4* dst = smem4 + (SLOT_WORDS + CAP) * RAYS * THREADS / 4;
+            const int n4 = PV.n_padded * 3 / 4;
+            for (int i = threadIdx.x; i < n4; i += THREADS) dst[i] = __ldg(&PV.s1[i]);
+            __syncthreads();
+        }
+    }
 
     const TraceConsts C = trace_consts(P);
     const unsigned lane = threadIdx.x & 31u;
@@ -744,7 +801,12 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
 #pragma unroll
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
-            sweep_two_stage<RAYS>(PV, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+            if constexpr (PV_T::s1_smem)
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt,
+                                      best_t, best_i);
+            else
+                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt,
+                                      best_t, best_i);
         } else {
             sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS,
                                             flt, best_t, best_i);

@@ -53,6 +53,8 @@ struct rtb200_ctx {
     std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsS<2560>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
+    float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
+    int n_padded = 32;
     int n_spheres = 0;
     // counters: [0] paths [1] segments [2] work counter
     unsigned long long* d_counters = nullptr;
@@ -164,6 +166,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV1024>;
     auto k_s512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS512>;
     auto k_s2560 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS2560>;
+    constexpr int LT = 512;                            // shared-memory two-stage variant: one 512-thread CTA per SM
+    auto k_sl = rtb::k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL>;
     auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
     auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
     if (!ctx->attrs_set) {
@@ -171,6 +175,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         CU_TRY(cudaFuncSetAttribute(k_v1024, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_s512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_s2560, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_sl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
@@ -187,6 +192,9 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const bool two_stage = fits_v && P.n_spheres <= 2560 && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
                            ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
     const bool use_v = fits_v && !two_stage && P.n_spheres <= 1024;
+    const size_t smem_sl = (size_t)(rtb::SLOT_WORDS + CV) * VR * LT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
+    const bool two_stage_smem = want != 1 && P.n_spheres > 2560 && smem_sl <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
+                                ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
     auto fill_s = [&](auto* ps) {
         ps->b = P;
         ps->up_axis = ctx->up_axis;
@@ -201,6 +209,11 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         auto* ps = reinterpret_cast<PS2560*>(ctx->h_params.data());
         fill_s(ps);
         k_s2560<<<sms * 4, VT, smem_v, st>>>(*ps);
+    } else if (two_stage_smem) {
+        rtb::TraceParamsL pl;
+        std::memset(&pl, 0, sizeof pl);
+        pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
+        k_sl<<<sms, LT, smem_sl, st>>>(pl);
     } else if (use_v && P.n_spheres <= 512) {
         auto* pv = reinterpret_cast<PV512*>(ctx->h_params.data());
         pv->b = P;
@@ -384,29 +397,6 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         mat[i] = make_float4((float)m.albedo[0], (float)m.albedo[1], (float)m.albedo[2], (float)param);
         kind[i] = m.kind | ((m.kind == RTB200_DIELECTRIC && m.hollow) ? RTB_HOLLOW_BIT : 0);
     }
-    CU_TRY(cudaSetDevice(ctx->device));
-    // One device arena [spheres | filter | materials | kinds], reused while it is large enough, filled by ONE copy.
-    const size_t bytes = cnt * (3 * sizeof(float4) + sizeof(int));
-    if (ctx->scene_capacity < bytes) {
-        cudaFree(ctx->d_scene);
-        ctx->d_scene = nullptr; ctx->scene_capacity = 0;
-        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr;
-        CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
-        ctx->scene_capacity = bytes;
-    }
-    std::vector<unsigned char> host(bytes);
-    std::memcpy(host.data(), sph.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + cnt * sizeof(float4), flt.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + 2 * cnt * sizeof(float4), mat.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + 3 * cnt * sizeof(float4), kind.data(), cnt * sizeof(int));
-    CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
-    unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
-    ctx->d_spheres = reinterpret_cast<float4*>(base);
-    ctx->d_filter = reinterpret_cast<float4*>(base + cnt * sizeof(float4));
-    ctx->d_mat = reinterpret_cast<float4*>(base + 2 * cnt * sizeof(float4));
-    ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
-    ctx->n_spheres = n;
-    ctx->h_filter.assign(flt.begin(), flt.begin() + n);
     {   // stage-1 data of the two-stage sweep: drop the axis along which the centres spread least (robust spread: the
         // 10%..90% range, so that one huge "ground" sphere does not decide), estimate how many pairs will pass
         int up = 1;
@@ -421,7 +411,7 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
             up = spread[0] <= spread[1] && spread[0] <= spread[2] ? 0 : (spread[1] <= spread[2] ? 1 : 2);
         }
         const int ia = (up + 1) % 3, ib = (up + 2) % 3;
-        const int padded = (n + 31) / 32 * 32;
+        const int padded = (int)cnt;
         ctx->h_slab.assign((size_t)padded * 3, 0.0f);
         const double extent = std::max(1e-30, 0.5 * (spread[ia] + spread[ib]));
         for (int i = 0; i < padded; i++) {
@@ -443,6 +433,32 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         ctx->up_axis = up;
         ctx->slab_pass = n > 0 ? pass / n : 1.0;
     }
+    CU_TRY(cudaSetDevice(ctx->device));
+    // One device arena [spheres | filter | materials | kinds | stage-1 triples], reused while it is large enough, filled by ONE copy.
+    const size_t bytes = cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float));
+    if (ctx->scene_capacity < bytes) {
+        cudaFree(ctx->d_scene);
+        ctx->d_scene = nullptr; ctx->scene_capacity = 0;
+        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr;
+        CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
+        ctx->scene_capacity = bytes;
+    }
+    std::vector<unsigned char> host(bytes);
+    std::memcpy(host.data(), sph.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + cnt * sizeof(float4), flt.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + 2 * cnt * sizeof(float4), mat.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + 3 * cnt * sizeof(float4), kind.data(), cnt * sizeof(int));
+    std::memcpy(host.data() + cnt * (3 * sizeof(float4) + sizeof(int)), ctx->h_slab.data(), cnt * 3 * sizeof(float));
+    CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
+    unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
+    ctx->d_spheres = reinterpret_cast<float4*>(base);
+    ctx->d_filter = reinterpret_cast<float4*>(base + cnt * sizeof(float4));
+    ctx->d_mat = reinterpret_cast<float4*>(base + 2 * cnt * sizeof(float4));
+    ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
+    ctx->d_slab = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int)));   // cnt % 32 == 0: 16-byte aligned
+    ctx->n_padded = (int)cnt;
+    ctx->n_spheres = n;
+    ctx->h_filter.assign(flt.begin(), flt.begin() + n);
     return RTB200_OK;
 }
 

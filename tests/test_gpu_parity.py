@@ -259,3 +259,21 @@ def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays, stages):
     assert np.abs(lin[..., :3].astype(np.float64) / 4 - ref_sum / 4).max() <= 1e-4
     assert stat.segments == ref_seg
     assert np.array_equal(img, ref_rgb)
+
+
+@pytest.mark.parametrize("rays,stages", VARIANTS)
+@pytest.mark.parametrize("half", [28, 50])
+def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, stages):
+    """Scenes beyond the parameter-space capacity (3 137 and 10 001 spheres): the shared-memory two-stage variant
+    (default), the resident one-stage variant (stages=1) and the one-ray resident variant against the oracle."""
+    scene = rtb.scenes._grid_scene(half, 77 + half, 0.6, 0.25, big=False)
+    W, H, spp = 96, 54, 2
+    renderer.rays_per_lane = rays
+    renderer.stages = stages
+    img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
+    renderer.rays_per_lane = 0
+    renderer.stages = 0
+    assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
+    assert stat.segments == ref_seg
+    assert stat.sphere_tests == ref_seg * len(scene)
+    assert np.array_equal(img, ref_rgb)
