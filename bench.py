@@ -246,7 +246,7 @@ def run_ours(args):
     # ---- end to end through Renderer.render with host buffers ------------------------------------------------
     e2e_steps = max(1, min(args.steps, 3))
     sc_abi, _keep = scene.to_abi()
-    h2d = n_spheres * (16 + 16 + 4)
+    h2d = (n_spheres + 31) // 32 * 32 * (16 + 16 + 16 + 4 + 12 + 32)   # the scene arena: exact | filter | material | kind | stage-1 triples | pairs
     d2h = W * H * 3
     if world == 1:
         out_img = renderer.pinned_empty((H, W, 3), np.uint8)   # the caller's image buffer: pinned host memory

@@ -299,46 +299,39 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
 // warps then advanced: lanes skipped blocks.)  The device arrays are padded to whole blocks with never-hit spheres, so
 // a padding bit that slips through stage 1 (NaN ray) is harmless.
 struct Best { float t; int i; };
+struct alignas(32) SpherePair { float4 filter, exact; };   // what stages 2 and 3 read for one sphere: one 32-byte record
 #ifndef RTB_REFINE_INLINE
 #define RTB_REFINE_INLINE __forceinline__   // two inlined copies (one per ray of the lane) beat one out-of-line copy by 5 %
 #endif
 
 __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
-                                          const float4* __restrict__ g_filter, const float4* __restrict__ g_exact, FilterRay f, ExactRay ray,
-                                          Best best) {
+                                          const SpherePair* __restrict__ g_pairs, FilterRay f, ExactRay ray, Best best) {
     if (todo == 0u) return best;
     const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                          // src/objects.rs:253
     const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
     uint32_t cand = 0;
-    int base = 0;
+    int last = 0;                                          // index of the block's sphere 31
     for (;;) {
         if (cand == 0u) {
             if (todo == 0u) break;
             const int b = __ffs(todo) - 1;
             todo &= todo - 1u;
             cand = ~masks_r[b * stride];                   // not empty: stage 1 set the block's bit
-            base = first_sphere + b * SWEEP_BLOCK;
+            last = first_sphere + b * SWEEP_BLOCK + (SWEEP_BLOCK - 1);
         }
-        const int j = __clz(cand);
-        cand &= ~(0x80000000u >> j);
-        const int idx = base + j;
-        const float4 fs = __ldg(&g_filter[idx]);
+        uint32_t hi, bit;                                  // sphere j of the block sits at bit 31 - j: highest bit first
+        asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));   // FLO / BMSK: ptxas otherwise rebuilds clz and 0x80000000 >> clz
+        asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
+        cand ^= bit;
+        const int idx = last - (int)hi;
+        const SpherePair* rec = g_pairs + idx;             // {filter, exact} of sphere idx
+        const float4 fs = __ldg(&rec->filter);
         const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2
-        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&g_exact[idx]), idx, best.t, best.i);   // stage 3
+        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&rec->exact), idx, best.t, best.i);   // stage 3
     }
     return best;
 }
 
-// The two-stage sweep of the parameter-space kernel.
-//   stage 1, all pairs, uniform control flow: the slab test (rt_filter.h: 3 FFMA, sphere operands in uniform
-//            registers, one funnel shift per pair) -> one 32-bit mask per 32-sphere block and ray, stored unconditionally
-//            (8 words per ray: the scene is swept in chunks of 8 blocks = 256 spheres), and a per-ray bit per block
-//            that holds a candidate;
-//   stage 2, lane-parallel over the stage-1 candidates of the chunk (a few per cent of the pairs), in sweep order: the
-//            8-instruction filter (filter_value), and for those that pass it
-//   stage 3, the reference's exact arithmetic (test_candidate).
-// Both filters are conservative, so the result equals the reference's sequential `update` over the object list.
-// masks layout: word b of ray r of this thread at masks[(r * 8 + b) * stride].
 // Stage-1 operand sources: evaluate the slab test of one 32-sphere block for the RAYS rays of a lane.
 // ParamSlab: {c_a, c_b, R'} triples in kernel parameter space -> LDCU.64 x3 per sphere pair, uniform-register operands.
 template <class PV_T>
@@ -381,8 +374,8 @@ struct SmemSlab {
 };
 
 template <int RAYS, class S1, class RaySrc>
-__device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const float4* __restrict__ g_filter,
-                                                const float4* __restrict__ g_exact, int count, uint32_t* masks, int stride,
+__device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const SpherePair* __restrict__ g_pairs, int count,
+                                                uint32_t* masks, int stride,
                                                 const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
@@ -408,7 +401,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -454,6 +447,7 @@ struct TraceParams {
     DeviceCamera cam;
     const float4* spheres;        // exact: {cx,cy,cz,r*r}
     const float4* filter;         // candidate filter: {cx,cy,cz,k} (rt_filter.h)
+    const float4* pairs;          // {filter, exact} interleaved per sphere: what stages 2 and 3 of the two-stage sweep read
     const float4* mat;            // per sphere {albedo rgb, param}
     const int* mat_kind;          // per sphere kind | hollow<<8
     int n_spheres;
@@ -802,11 +796,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             if constexpr (PV_T::s1_smem)
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt,
-                                      best_t, best_i);
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
             else
-                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st}, P.filter, P.spheres, P.n_spheres, list, THREADS, slab, flt,
-                                      best_t, best_i);
+                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab,
+                                      flt, best_t, best_i);
         } else {
             sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS,
                                             flt, best_t, best_i);

@@ -53,6 +53,7 @@ struct rtb200_ctx {
     std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsS<2560>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
+    float4* d_pairs = nullptr;                         // {filter, exact} interleaved per sphere (two-stage refine walk)
     float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
     int n_padded = 32;
     int n_spheres = 0;
@@ -127,7 +128,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const int n_samples = p->sample_end - p->sample_begin;
     rtb::TraceParams P;
     P.cam = device_camera(*cam);
-    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
+    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.pairs = ctx->d_pairs; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
     P.n_spheres = ctx->n_spheres;
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
@@ -434,12 +435,12 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         ctx->slab_pass = n > 0 ? pass / n : 1.0;
     }
     CU_TRY(cudaSetDevice(ctx->device));
-    // One device arena [spheres | filter | materials | kinds | stage-1 triples], reused while it is large enough, filled by ONE copy.
-    const size_t bytes = cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float));
+    // One device arena [spheres | filter | materials | kinds | stage-1 triples | {filter, exact} pairs], reused while it is large enough, filled by ONE copy.
+    const size_t bytes = cnt * (5 * sizeof(float4) + sizeof(int) + 3 * sizeof(float));
     if (ctx->scene_capacity < bytes) {
         cudaFree(ctx->d_scene);
         ctx->d_scene = nullptr; ctx->scene_capacity = 0;
-        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr;
+        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr; ctx->d_pairs = nullptr;
         CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
         ctx->scene_capacity = bytes;
     }
@@ -449,6 +450,10 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     std::memcpy(host.data() + 2 * cnt * sizeof(float4), mat.data(), cnt * sizeof(float4));
     std::memcpy(host.data() + 3 * cnt * sizeof(float4), kind.data(), cnt * sizeof(int));
     std::memcpy(host.data() + cnt * (3 * sizeof(float4) + sizeof(int)), ctx->h_slab.data(), cnt * 3 * sizeof(float));
+    {
+        float4* pr = reinterpret_cast<float4*>(host.data() + cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float)));
+        for (size_t i = 0; i < cnt; i++) { pr[2 * i] = flt[i]; pr[2 * i + 1] = sph[i]; }
+    }
     CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
     unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
     ctx->d_spheres = reinterpret_cast<float4*>(base);
@@ -456,6 +461,7 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     ctx->d_mat = reinterpret_cast<float4*>(base + 2 * cnt * sizeof(float4));
     ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
     ctx->d_slab = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int)));   // cnt % 32 == 0: 16-byte aligned
+    ctx->d_pairs = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float)));
     ctx->n_padded = (int)cnt;
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);

@@ -178,7 +178,13 @@ class Scene:
 
     # ---- flattening to the C ABI -----------------------------------------------------------------------
     def to_abi(self):
-        """Returns (rtb200_scene, keepalive) — AoS arrays in object order, materials in table order."""
+        """Returns (rtb200_scene, keepalive) — AoS arrays in object order, materials in table order.  The flattening is
+        done once per Scene (the reference builds its Vec<Object> once in Scene::from_list, src/ray_tracing.rs:299-306);
+        a Scene whose object or material count changed is flattened again."""
+        key = (len(self.objects), len(self.materials))
+        cached = self.__dict__.get("_abi_cache")
+        if cached is not None and cached[0] == key:
+            return cached[1], cached[2]
         names = list(self.materials.keys())
         index = {n: i for i, n in enumerate(names)}
         mats = (_abi.Material * max(1, len(names)))()
@@ -194,6 +200,7 @@ class Scene:
             sph[i].radius = s.radius
             sph[i].material = index[s.material]
         sc = _abi.Scene(C.cast(sph, C.POINTER(_abi.Sphere)), len(self.objects), C.cast(mats, C.POINTER(_abi.Material)), len(names))
+        self.__dict__["_abi_cache"] = (key, sc, (sph, mats))
         return sc, (sph, mats)
 
     def arrays(self):
