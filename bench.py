@@ -152,7 +152,7 @@ def run_reference(args):
         "e2e": {"value": res["mpaths_s"], "unit": "Mpaths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -316,13 +316,29 @@ def run_ours(args):
             "clocks": clocks,
             "cpu_baseline": cpu,
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_json_out = None
+
+
+def emit(line: dict) -> None:
+    """The ONE stdout line of the contract."""
+    out = _json_out if _json_out is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    # Libraries (NCCL prints its version banner) write to file descriptor 1: keep the real stdout for the JSON line
+    # and send everything else to stderr.
+    global _json_out
+    sys.stdout.flush()
+    _json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
