@@ -84,10 +84,13 @@ typedef struct rtb200_params {
 } rtb200_params;
 
 #define RTB200_FLAG_NONE 0
-#define RTB200_FLAG_RAYS1 1 /* force the one-ray-per-lane trace kernel  */
-#define RTB200_FLAG_RAYS2 2 /* force the two-rays-per-lane (parameter-space) trace kernel */
-#define RTB200_FLAG_ONE_STAGE 4 /* parameter-space kernel: all pairs through the 8-instruction filter (no slab stage) */
-#define RTB200_FLAG_TWO_STAGE 8 /* parameter-space kernel: force the slab stage even where the scene layout does not favour it */
+/* Kernel-variant overrides (the parity tests run every variant; 0 lets the library choose from the scene):        */
+#define RTB200_FLAG_RAYS1 1 /* force the one-ray-per-lane resident trace kernel (one-stage sweep, spheres in shared memory) */
+#define RTB200_FLAG_RAYS2 2 /* force the two-slots-per-lane trace kernels                                                  */
+#define RTB200_FLAG_ONE_STAGE 4 /* all pairs through the 8-instruction filter (no slab stage)                               */
+#define RTB200_FLAG_TWO_STAGE 8 /* force the slab stage (3-FFMA all-pairs test, then filter, then the exact arithmetic) even
+                                   where the scene layout does not favour it; <= 2560 spheres from parameter space, beyond
+                                   that from shared memory                                                              */
 
 /* Mirror of RenderStat (src/renderer.rs:11-34) plus the counters the metric needs. */
 typedef struct rtb200_stats {
