@@ -92,6 +92,17 @@ typedef struct rtb200_params {
                                    where the scene layout does not favour it; <= 2560 spheres from parameter space, beyond
                                    that from shared memory                                                              */
 
+#define RTB200_FLAG_BOTH_ROOTS 16 /* this call only: RTB200_HIT_BOTH_ROOTS (see rtb200_set_hit_mode) */
+
+/* Hit modes.  NEAR_ROOT is what the reference's live renderer does: Sphere::hit_packed derives root2's validity from
+ * root1 (src/objects.rs:272-276), so only the near root ever counts and a ray that starts inside a sphere misses it
+ *  — glass spheres do not refract a second time on the way out.  BOTH_ROOTS applies the rule of the
+ * reference's scalar Sphere::hit (src/objects.rs:227-234) inside the same packed arithmetic: when the near root is
+ * outside [0.001, inf) the far root is tried.  It is NOT what the reference's binary renders; it is the physically
+ * right dielectric.  Parity for it is against the oracle run with the same option. */
+#define RTB200_HIT_NEAR_ROOT 0
+#define RTB200_HIT_BOTH_ROOTS 1
+
 /* Mirror of RenderStat (src/renderer.rs:11-34) plus the counters the metric needs. */
 typedef struct rtb200_stats {
     double seconds;             /* RenderStat::duration — wall time of the call                      */
@@ -193,6 +204,10 @@ int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, 
 
 /* Device counters of the last trace on this context (valid after the stream has been synchronised). */
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
+
+/* Selects the hit mode (RTB200_HIT_*) of every later rtb200_render / rtb200_trace_device / rtb200_intersect_batch on
+ * this context.  Default RTB200_HIT_NEAR_ROOT. */
+int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode);
 
 /* Number of kernel launches this context has issued since creation (trace, resolve, intersect, probe). */
 int64_t rtb200_launch_count(rtb200_ctx* ctx);

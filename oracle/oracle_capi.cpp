@@ -13,11 +13,15 @@ using namespace rto;
 
 namespace {
 
+// Hit mode of the scenes built after the call (oracle_set_both_roots): false = the reference's packed path.
+static bool g_both_roots = false;
+
 template <class R>
 Scene<R> make_scene(const double* spheres /*[n][4] cx cy cz r*/, const int32_t* sphere_material, int32_t n,
                     const int32_t* mat_kind, const int32_t* mat_hollow, const double* mat_albedo /*[m][3]*/,
                     const double* mat_param, int32_t m) {
     Scene<R> s;
+    s.both_roots = g_both_roots;
     s.spheres.resize(n);
     for (int32_t i = 0; i < n; i++) {
         s.spheres[i].center = {(R)spheres[4 * i + 0], (R)spheres[4 * i + 1], (R)spheres[4 * i + 2]};
@@ -89,6 +93,10 @@ void render_impl(const Scene<R>& scene, const CameraD& camd, int32_t s0, int32_t
 }  // namespace
 
 extern "C" {
+
+// 0 (default): near root only, as the reference's live renderer; 1: the scalar Sphere::hit rule (rt_oracle.hpp sweep).
+// Process-wide; the test harness sets it around a call.
+void oracle_set_both_roots(int32_t on) { g_both_roots = on != 0; }
 
 void oracle_philox4x32_10(const uint32_t* ctr4, const uint32_t* key2, uint32_t* out4) {
     Philox4 p = philox4x32_10(ctr4[0], ctr4[1], ctr4[2], ctr4[3], key2[0], key2[1]);

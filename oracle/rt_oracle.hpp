@@ -171,7 +171,7 @@ template <class R> struct Material {
     R param;          // metal: fuzzy_factor (already clamped to <= 1, materials.rs:79-88); dielectric: index_of_refraction
 };
 template <class R> struct Sphere { V3<R> center; R radius; int32_t material; };
-template <class R> struct Scene { std::vector<Sphere<R>> spheres; std::vector<Material<R>> materials; };
+template <class R> struct Scene { std::vector<Sphere<R>> spheres; std::vector<Material<R>> materials; bool both_roots = false; };
 
 template <class R> struct Ray { V3<R> o, d; };   // src/ray.rs:5-18 — direction stored as given, never normalised
 
@@ -261,6 +261,9 @@ template <class R> inline R sphere_discriminant(const Sphere<R>& s, const Ray<R>
     return std::fma(half_b, half_b, -(a * c));                     // :257
 }
 
+// scene.both_roots (NOT the reference's live path; rtb200's RTB200_HIT_BOTH_ROOTS option): the rule of the scalar
+// Sphere::hit (src/objects.rs:227-234) inside the packed arithmetic — when root1 is outside the range, root2 (:271) is
+// tried.
 template <class R> inline SweepHit<R> sweep(const Scene<R>& scene, const Ray<R>& ray, bool enabled = true) {
     const R T_MIN = (R)0.001;
     const R INF = std::numeric_limits<R>::infinity();
@@ -274,6 +277,10 @@ template <class R> inline SweepHit<R> sweep(const Scene<R>& scene, const Ray<R>&
             R sq = std::sqrt(disc);                                // :263
             R root1 = (-half_b - sq) * inv_a;                      // :270
             bool valid = (root1 >= T_MIN) && (root1 < INF) && enabled;   // :272-277
+            if (!valid && scene.both_roots) {                      // scalar rule, :230-234
+                root1 = (-half_b + sq) * inv_a;                    // :271
+                valid = (root1 >= T_MIN) && (root1 < INF) && enabled;
+            }
             if (valid && root1 <= best.t) {                        // update_mask, :141
                 best.hit = true; best.index = i; best.t = root1;   // :143-147
             }

@@ -30,6 +30,8 @@ void usage() {
         "  --focal-length F --view-angle DEG --defocus-angle DEG               [10, 30, 0]\n"
         "  --center X,Y,Z --look-at X,Y,Z --up X,Y,Z                           [16,2,18.5  0,0,0  0,1,0]\n"
         "  --camera-from-scene     use the scene file's [camera] table (Camera::from_toml keys)\n"
+        "  --both-roots            scalar Sphere::hit rule (far root when the near one is out of range): physically right\n"
+        "                          glass; NOT what the reference's packed renderer draws\n"
         "  --dump-toml             print the parsed TOML document as JSON and exit (no GPU)\n"
         "  --dump-scene            print the flattened scene as JSON and exit (no GPU)\n"
         "  --dump-camera           print the derived camera (Camera::new) as JSON and exit (no GPU)\n"
@@ -55,6 +57,7 @@ int main(int argc, char** argv) {
     int spp = 100, depth = 50, device = 0;                              // src/main.rs:64
     unsigned long long seed = 1;
     bool dump_toml = false, dump_scene = false, dump_camera = false, stats_json = false, quiet = false, camera_from_scene = false;
+    bool both_roots = false;
     bool have_scene_arg = false;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
@@ -77,6 +80,7 @@ int main(int argc, char** argv) {
         else if (a == "--look-at") { if (!parse3(need("--look-at"), cam.look_at)) { std::fprintf(stderr, "rtb200_cli: --look-at wants X,Y,Z\n"); return 2; } }
         else if (a == "--up") { if (!parse3(need("--up"), cam.up)) { std::fprintf(stderr, "rtb200_cli: --up wants X,Y,Z\n"); return 2; } }
         else if (a == "--camera-from-scene") camera_from_scene = true;
+        else if (a == "--both-roots") both_roots = true;
         else if (a == "--dump-toml") dump_toml = true;
         else if (a == "--dump-scene") dump_scene = true;
         else if (a == "--dump-camera") dump_camera = true;
@@ -134,6 +138,7 @@ int main(int argc, char** argv) {
         return 1;
     };
     if (rtb200_create(device, &ctx) != RTB200_OK) return die("rtb200_create");           // TileRenderer::new, src/main.rs:62
+    if (both_roots && rtb200_set_hit_mode(ctx, RTB200_HIT_BOTH_ROOTS) != RTB200_OK) return die("rtb200_set_hit_mode");
     rtb200_scene abi = scene.abi();
     if (rtb200_upload_scene(ctx, &abi) != RTB200_OK) return die("rtb200_upload_scene");  // Scene::from_list, src/main.rs:43
     rtb200_params params;

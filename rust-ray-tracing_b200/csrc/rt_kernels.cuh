@@ -37,11 +37,13 @@ __device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __res
 }
 
 // One ray as the exact candidate test needs it (origin, direction as stored: never normalised, src/ray.rs:13-18).
-struct ExactRay { float ox, oy, oz, dx, dy, dz; };
+// both_roots: warp-uniform hit mode (false = the reference's packed path: near root only; true = the scalar
+// Sphere::hit rule, src/objects.rs:227-234: the far root when the near one is out of range).
+struct ExactRay { float ox, oy, oz, dx, dy, dz; bool both_roots; };
 
-__device__ __forceinline__ ExactRay make_exact_ray(f3 o, f3 d) {
+__device__ __forceinline__ ExactRay make_exact_ray(f3 o, f3 d, bool both_roots) {
     ExactRay r;
-    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.both_roots = both_roots;
     return r;
 }
 // The ray's half of the candidate filter; a = d.d as the sweep computes it (src/objects.rs:253).
@@ -65,6 +67,10 @@ __device__ __forceinline__ void test_candidate(const ExactRay& r, float a, float
         float sq = __fsqrt_rn(disc);                                                               // :263
         float root1 = __fmul_rn(__fsub_rn(-hb, sq), inv_a);                                        // :270
         bool valid = (root1 >= T_MIN) && (root1 < RTB_INF);                                        // :272-277 (near root only, F4)
+        if (!valid && r.both_roots) {                                                              // scalar Sphere::hit, :230-234
+            root1 = __fmul_rn(__fadd_rn(-hb, sq), inv_a);                                          // :271
+            valid = (root1 >= T_MIN) && (root1 < RTB_INF);
+        }
         if (valid && root1 <= best_t) { best_t = root1; best_i = index; }                          // :141 (`<=`: last wins, F5)
     }
 }
@@ -416,7 +422,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
                                                          const float* __restrict__ oz, const float* __restrict__ dx,
                                                          const float* __restrict__ dy, const float* __restrict__ dz,
                                                          const uint8_t* __restrict__ enabled, long long n_rays,
-                                                         int* __restrict__ hit_index, float* __restrict__ hit_t) {
+                                                         int* __restrict__ hit_index, float* __restrict__ hit_t, int both_roots) {
     extern __shared__ float4 smem4[];
     float4* s_sph = smem4;
     uint2* list = reinterpret_cast<uint2*>(smem4 + tile) + threadIdx.x;
@@ -424,7 +430,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     bool live = i < n_rays;
     f3 o = mk3(0.f, 0.f, 0.f), d = mk3(0.f, 0.f, 1.f);
     if (live) { o = mk3(ox[i], oy[i], oz[i]); d = mk3(dx[i], dy[i], dz[i]); }
-    ExactRay ray[1] = {make_exact_ray(o, d)};
+    ExactRay ray[1] = {make_exact_ray(o, d, both_roots != 0)};
     FilterRay flt[1] = {make_filter(o, d)};
     float best_t[1] = {RTB_INF};                               // PackedHitRecords::default, src/objects.rs:121-134
     int best_i[1] = {-1};
@@ -455,6 +461,7 @@ struct TraceParams {
     uint32_t seed_lo, seed_hi;
     int sample_begin, sample_end; // global sample indices traced by this launch
     int row_begin, row_end;
+    int both_roots;               // hit mode: 0 = near root only (the reference's packed path), 1 = scalar Sphere::hit rule
     int splits_log2;              // K = 1 << splits_log2: the sample range is cut into K contiguous sub-ranges, one work item each
     uint32_t width_magic;         // floor(2^32 / W) + 1 (0 when W == 1): row = pixel / W by multiply-high
     float4* out;                  // K == 1: accum image (W*H float4); else partial planes [K][rows*W]
@@ -692,7 +699,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         FilterRay flt[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            ray[r] = make_exact_ray(slot[r].o, slot[r].d);
+            ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
             flt[r] = make_filter(slot[r].o, slot[r].d);
             best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
             best_i[r] = -1;
@@ -715,8 +722,10 @@ constexpr int SLOT_WORDS = 17;   // o 0-2, d 3-5, thr 6-8, acc 9-11, item 12, s 
 template <int RAYS, int THREADS>
 struct SmemRays {
     const uint32_t* st;
+    bool both_roots;
     __device__ __forceinline__ ExactRay load(int r) const {
         ExactRay e;
+        e.both_roots = both_roots;
         e.ox = __uint_as_float(st[(0 * RAYS + r) * THREADS]); e.oy = __uint_as_float(st[(1 * RAYS + r) * THREADS]);
         e.oz = __uint_as_float(st[(2 * RAYS + r) * THREADS]); e.dx = __uint_as_float(st[(3 * RAYS + r) * THREADS]);
         e.dy = __uint_as_float(st[(4 * RAYS + r) * THREADS]); e.dz = __uint_as_float(st[(5 * RAYS + r) * THREADS]);
@@ -796,12 +805,12 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             if constexpr (PV_T::s1_smem)
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
             else
-                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab,
+                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab,
                                       flt, best_t, best_i);
         } else {
-            sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st}, P.spheres, P.n_spheres, list, THREADS,
+            sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.spheres, P.n_spheres, list, THREADS,
                                             flt, best_t, best_i);
         }
 #pragma unroll

@@ -47,6 +47,7 @@ struct rtb200_ctx {
     float4* d_filter = nullptr;
     std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
     std::vector<float> h_slab;                         // stage-1 spheres {c_a, c_b, R'} padded to whole 32-blocks (two-stage variant)
+    int hit_mode = 0;                                  // RTB200_HIT_*
     int up_axis = 1;                                   // the axis the slab test drops
     float slab_rp_min = 1.0f;                          // smallest floored R' of the scene (rt_filter.h make_slab_ray)
     double slab_pass = 1.0;                            // estimated fraction of pairs that pass stage 1
@@ -134,6 +135,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
     P.sample_begin = p->sample_begin; P.sample_end = p->sample_end;
     P.row_begin = p->row_begin; P.row_end = p->row_end;
+    P.both_roots = (ctx->hit_mode == RTB200_HIT_BOTH_ROOTS || (p->flags & RTB200_FLAG_BOTH_ROOTS)) ? 1 : 0;
     P.splits_log2 = choose_splits_log2(ctx, n_pix, n_samples);
     const int splits = 1 << P.splits_log2;
     P.width_magic = W > 1 ? (uint32_t)((1ull << 32) / (unsigned long long)W) + 1u : 0u;
@@ -268,7 +270,8 @@ int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const fl
     }
     long long blocks = (n + threads - 1) / threads;
     if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
-    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->d_filter, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t);
+    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->d_filter, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t,
+                                                                  ctx->hit_mode == RTB200_HIT_BOTH_ROOTS ? 1 : 0);
     CU_TRY(cudaGetLastError());
     ctx->launches++;
     return RTB200_OK;
@@ -648,6 +651,13 @@ int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
 }
 
 int64_t rtb200_launch_count(rtb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "null context");
+    if (mode != RTB200_HIT_NEAR_ROOT && mode != RTB200_HIT_BOTH_ROOTS) return fail(RTB200_ERR_INVALID, "unknown hit mode " + std::to_string(mode));
+    ctx->hit_mode = mode;
+    return RTB200_OK;
+}
 
 int rtb200_fp32_peak(rtb200_ctx* ctx, int32_t iters, double* tflops, double* ms_out) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");

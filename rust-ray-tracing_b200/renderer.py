@@ -101,6 +101,12 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_fp32_peak(self._ctx, int(iters), C.byref(tf), C.byref(ms)))
         return tf.value, ms.value
 
+    def set_hit_mode(self, both_roots: bool) -> None:
+        """False (default): the reference's packed path — near root only (src/objects.rs:272-276).
+        True: the scalar Sphere::hit rule (src/objects.rs:227-234) — the far root when the near one is out of range,
+        i.e. rays inside a glass sphere hit its far wall.  Not what the reference's binary renders."""
+        _abi.check(_abi.lib.rtb200_set_hit_mode(self._ctx, 1 if both_roots else 0))
+
     # ---- scene ---------------------------------------------------------------------------------------------
     def upload_scene(self, scene: Scene) -> None:
         sc, keep = scene.to_abi()

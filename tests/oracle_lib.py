@@ -71,6 +71,11 @@ def camera_get_ray(width, height, cam18, col, row, rnd4, f32: bool):
     return np.array(out[:])
 
 
+def set_both_roots(on: bool) -> None:
+    """Hit mode of later intersect()/render() calls: False = the reference's packed path (near root only)."""
+    _lib.oracle_set_both_roots(1 if on else 0)
+
+
 def intersect(spheres, rays, enabled=None, f32: bool = True):
     """spheres [n,4] (cx,cy,cz,r) f64; rays [m,6] f64 -> (idx[m] i32, t[m] f64)."""
     sp = np.ascontiguousarray(spheres, dtype=np.float64).reshape(-1, 4)

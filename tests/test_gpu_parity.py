@@ -277,3 +277,53 @@ def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, st
     assert stat.segments == ref_seg
     assert stat.sphere_tests == ref_seg * len(scene)
     assert np.array_equal(img, ref_rgb)
+
+
+def test_both_roots_intersect(rtb, renderer, oracle):
+    """RTB200_HIT_BOTH_ROOTS (scalar Sphere::hit rule) on the GPU against the oracle with the same option."""
+    S, M = rtb.Sphere, rtb.Material
+    one = rtb.Scene.from_list([S((0.0, 0.0, -1.0), 0.5, "m")], {"m": M.lambertian((0.5, 0.5, 0.5))})
+    o = np.array([[0, 0, -1], [0, 0, -0.5], [0, 0, 0], [0, 0, -2]], dtype=np.float32)
+    d = np.array([[0, 0, -1]] * 4, dtype=np.float32)
+    renderer.set_hit_mode(True)
+    oracle.set_both_roots(True)
+    try:
+        idx, t = renderer.intersect_batch(one, o, d)
+        assert list(idx) == [0, 0, 0, -1] and t[0] == np.float32(0.5) and t[1] == np.float32(1.0)
+        scene = rtb.scenes.dielectric_heavy()
+        rng = np.random.default_rng(11)
+        oo, dd = _rays(rng, 20000, scene.arrays())
+        sp = scene.arrays()[0]
+        pick = sp[rng.integers(1, len(sp), size=10000)]      # half of the rays start INSIDE a sphere (not the ground)
+        oo[:10000] = (pick[:, :3] + 0.5 * pick[:, 3:4] * rng.uniform(-0.5, 0.5, size=(10000, 3))).astype(np.float32)
+        idx, _ = _check_intersect(renderer, oracle, scene, oo, dd)
+        assert (idx[:10000] >= 0).all()                      # from inside, the far wall is always hit
+    finally:
+        renderer.set_hit_mode(False)
+        oracle.set_both_roots(False)
+    idx, _ = renderer.intersect_batch(one, o, d)
+    assert list(idx) == [-1, -1, 0, -1]                      # default mode restored: near root only (F4)
+
+
+@pytest.mark.parametrize("rays,stages", VARIANTS)
+@pytest.mark.parametrize("scene_name", ["three_spheres", "dielectric_heavy"])
+def test_both_roots_render_matches_oracle(rtb, renderer, oracle, scene_name, rays, stages):
+    scene = getattr(rtb.scenes, scene_name)()
+    W, H, spp = 160, 90, 8
+    renderer.rays_per_lane = rays
+    renderer.stages = stages
+    renderer.set_hit_mode(True)
+    oracle.set_both_roots(True)
+    try:
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
+    finally:
+        renderer.set_hit_mode(False)
+        oracle.set_both_roots(False)
+        renderer.rays_per_lane = 0
+        renderer.stages = 0
+    assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
+    assert stat.segments == ref_seg
+    assert np.array_equal(img, ref_rgb)
+    # and it is a different image from the reference's near-root-only rendering (glass refracts on the way out)
+    img0, _ = renderer.render(50, spp, scene, rtb.Camera.default(W, H))
+    assert not np.array_equal(img, img0)

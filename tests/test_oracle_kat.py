@@ -235,3 +235,23 @@ def test_cpu_baseline_port_agrees_with_per_path_oracle(oracle, rtb):
     # rows outside the requested range are left untouched
     part, _, _, _ = oracle.cpuref_render(scene.arrays(), W, H, cam.vectors(), 4, 50, threads=2, row_range=(10, 20))
     assert np.all(part[:10] == 0) and np.all(part[20:] == 0) and part[10:20].any()
+
+
+def test_both_roots_option_is_the_scalar_rule(oracle):
+    """RTB200_HIT_BOTH_ROOTS: the scalar Sphere::hit rule (src/objects.rs:227-234) — far root when the near one is out of
+    range.  Default stays the packed path (near root only)."""
+    sph = np.array([[0.0, 0.0, -1.0, 0.5]])
+    rays = np.array([[0, 0, -1, 0, 0, -1],       # from the centre: near -0.5, far +0.5
+                     [0, 0, -0.5, 0, 0, -1],     # on the near surface looking in: near 0 (< 0.001), far 1.0
+                     [0, 0, 0, 0, 0, -1],        # outside: near root valid, unchanged
+                     [0, 0, -2, 0, 0, -1]], dtype=np.float64)   # behind the sphere looking away: both roots negative
+    for f32 in (False, True):
+        idx, t = oracle.intersect(sph, rays, f32=f32)
+        assert list(idx) == [-1, -1, 0, -1]
+        oracle.set_both_roots(True)
+        try:
+            idx, t = oracle.intersect(sph, rays, f32=f32)
+        finally:
+            oracle.set_both_roots(False)
+        assert list(idx) == [0, 0, 0, -1]
+        assert t[0] == 0.5 and t[1] == 1.0 and t[2] == 0.5 and np.isinf(t[3])
