@@ -205,6 +205,14 @@ int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, 
 /* Device counters of the last trace on this context (valid after the stream has been synchronised). */
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
 
+/* Progress reporting (the reference redraws a per-tile progress grid on stderr while it renders,
+ * src/renderer.rs:300-365; here it is a callback, off by default).  While rtb200_render waits for the trace kernel it
+ * calls fn(user, items_claimed, items_total, elapsed_seconds) every interval_ms milliseconds from the calling thread,
+ * and once more with items_claimed == items_total when the kernel has finished.  A work item is one pixel's share of
+ * the sample range (what a path slot claims from the device work queue).  fn == NULL switches it off. */
+typedef void (*rtb200_progress_fn)(void* user, uint64_t items_claimed, uint64_t items_total, double elapsed_seconds);
+int rtb200_set_progress(rtb200_ctx* ctx, rtb200_progress_fn fn, void* user, int32_t interval_ms);
+
 /* Selects the hit mode (RTB200_HIT_*) of every later rtb200_render / rtb200_trace_device / rtb200_intersect_batch on
  * this context.  Default RTB200_HIT_NEAR_ROOT. */
 int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode);

@@ -73,6 +73,7 @@ SYMBOLS = {
     "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtb200_launch_count": (C.c_int64, [_P]),
     "rtb200_set_hit_mode": (C.c_int32, [_P, C.c_int32]),
+    "rtb200_set_progress": (C.c_int32, [_P, C.c_void_p, C.c_void_p, C.c_int32]),
     "rtb200_fp32_peak": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
 

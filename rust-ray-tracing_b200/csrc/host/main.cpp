@@ -35,6 +35,7 @@ void usage() {
         "  --dump-toml             print the parsed TOML document as JSON and exit (no GPU)\n"
         "  --dump-scene            print the flattened scene as JSON and exit (no GPU)\n"
         "  --dump-camera           print the derived camera (Camera::new) as JSON and exit (no GPU)\n"
+        "  --progress              redraw a progress line on stderr while rendering (the reference's progress grid)\n"
         "  --stats-json            also print the render statistics as one JSON line\n"
         "  --quiet                 no summary lines");
 }
@@ -57,7 +58,7 @@ int main(int argc, char** argv) {
     int spp = 100, depth = 50, device = 0;                              // src/main.rs:64
     unsigned long long seed = 1;
     bool dump_toml = false, dump_scene = false, dump_camera = false, stats_json = false, quiet = false, camera_from_scene = false;
-    bool both_roots = false;
+    bool both_roots = false, progress = false;
     bool have_scene_arg = false;
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
@@ -81,6 +82,7 @@ int main(int argc, char** argv) {
         else if (a == "--up") { if (!parse3(need("--up"), cam.up)) { std::fprintf(stderr, "rtb200_cli: --up wants X,Y,Z\n"); return 2; } }
         else if (a == "--camera-from-scene") camera_from_scene = true;
         else if (a == "--both-roots") both_roots = true;
+        else if (a == "--progress") progress = true;
         else if (a == "--dump-toml") dump_toml = true;
         else if (a == "--dump-scene") dump_scene = true;
         else if (a == "--dump-camera") dump_camera = true;
@@ -139,6 +141,20 @@ int main(int argc, char** argv) {
     };
     if (rtb200_create(device, &ctx) != RTB200_OK) return die("rtb200_create");           // TileRenderer::new, src/main.rs:62
     if (both_roots && rtb200_set_hit_mode(ctx, RTB200_HIT_BOTH_ROOTS) != RTB200_OK) return die("rtb200_set_hit_mode");
+    if (progress) {   // src/renderer.rs:300-365 draws a tile grid; one line is enough for a render that takes milliseconds to seconds
+        auto draw = [](void*, uint64_t done, uint64_t total, double secs) {
+            const double frac = total ? (double)done / (double)total : 1.0;
+            const double eta = frac > 0.0 ? secs * (1.0 - frac) / frac : 0.0;
+            char bar[41];
+            const int fill = (int)(frac * 40.0);
+            for (int i = 0; i < 40; i++) bar[i] = i < fill ? '#' : '.';
+            bar[40] = 0;
+            std::fprintf(stderr, "\r[%s] %5.1f %%  %.2f s elapsed, ETA %.2f s ", bar, 100.0 * frac, secs, eta);
+            if (done == total) std::fputc('\n', stderr);
+            std::fflush(stderr);
+        };
+        if (rtb200_set_progress(ctx, draw, nullptr, 100) != RTB200_OK) return die("rtb200_set_progress");
+    }
     rtb200_scene abi = scene.abi();
     if (rtb200_upload_scene(ctx, &abi) != RTB200_OK) return die("rtb200_upload_scene");  // Scene::from_list, src/main.rs:43
     rtb200_params params;

@@ -466,6 +466,7 @@ struct TraceParams {
     uint32_t width_magic;         // floor(2^32 / W) + 1 (0 when W == 1): row = pixel / W by multiply-high
     float4* out;                  // K == 1: accum image (W*H float4); else partial planes [K][rows*W]
     unsigned long long* work_counter;
+    unsigned long long* progress; // mapped pinned host memory (or null): the queue head, published every 4096 items
     unsigned long long* counters; // [0] paths, [1] segments
 };
 
@@ -590,7 +591,12 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     const unsigned need_mask = __ballot_sync(0xffffffffu, q.item == NO_ITEM && !exhausted);
     if (need_mask) {
         unsigned long long base64 = 0;
-        if (lane == 0) base64 = atomicAdd(P.work_counter, (unsigned long long)__popc(need_mask));
+        if (lane == 0) {
+            const unsigned long long n_claim = (unsigned long long)__popc(need_mask);
+            base64 = atomicAdd(P.work_counter, n_claim);
+            // progress for the host (rtb200_set_progress): every 4096 items the new queue head goes to mapped host memory
+            if (P.progress && ((base64 ^ (base64 + n_claim)) >> 12)) *reinterpret_cast<volatile unsigned long long*>(P.progress) = base64 + n_claim;
+        }
         base64 = __shfl_sync(0xffffffffu, base64, 0);
         // items beyond n_items (< 2^32) saturate: the queue head only ever overshoots by the number of lanes
         const uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -48,6 +49,12 @@ struct rtb200_ctx {
     std::vector<float4> h_filter;                      // host copy of the filter spheres (kernel-parameter variant)
     std::vector<float> h_slab;                         // stage-1 spheres {c_a, c_b, R'} padded to whole 32-blocks (two-stage variant)
     int hit_mode = 0;                                  // RTB200_HIT_*
+    rtb200_progress_fn progress_cb = nullptr;          // rtb200_set_progress
+    void* progress_user = nullptr;
+    int progress_interval_ms = 100;
+    unsigned long long* h_progress = nullptr;          // mapped pinned host memory: the kernel publishes its queue head here
+    unsigned long long* d_progress = nullptr;          // its device-side address
+    unsigned long long items_total = 0;                // work items of the last trace launch
     int up_axis = 1;                                   // the axis the slab test drops
     float slab_rp_min = 1.0f;                          // smallest floored R' of the scene (rt_filter.h make_slab_ray)
     double slab_pass = 1.0;                            // estimated fraction of pairs that pass stage 1
@@ -140,6 +147,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const int splits = 1 << P.splits_log2;
     P.width_magic = W > 1 ? (uint32_t)((1ull << 32) / (unsigned long long)W) + 1u : 0u;
     P.work_counter = ctx->d_counters + 2;
+    P.progress = (ctx->progress_cb && ctx->h_progress) ? ctx->d_progress : nullptr;
+    if (ctx->h_progress) *ctx->h_progress = 0ull;
     P.counters = ctx->d_counters;
     if (splits > 1) {
         size_t want = (size_t)splits * (size_t)n_pix;
@@ -155,6 +164,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     }
     if ((unsigned long long)n_pix * (unsigned long long)splits >= (1ull << 32) - 65536)
         return fail(RTB200_ERR_INVALID, "too many work items for one launch");
+    ctx->items_total = (unsigned long long)n_pix * (unsigned long long)splits;
     // Kernel variants.
     //   v  : k_trace_paths_v<threads, CTAs/SM, rays per lane, list capacity, N> — filter spheres in parameter space, path
     //        state in shared memory; scenes of at most N spheres (N = 512 or 1024: up to 16 KB of kernel parameters).
@@ -317,6 +327,7 @@ void rtb200_destroy(rtb200_ctx* c) {
     cudaFree(c->d_scene); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->h_progress) cudaFreeHost(c->h_progress);
     delete c;
 }
 
@@ -551,6 +562,29 @@ int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_par
     rc = launch_trace(ctx, camera, params, ctx->d_accum, st);
     if (rc) return rc;
     CU_TRY(cudaEventRecord(ctx->ev[1], st));
+    if (ctx->progress_cb && ctx->h_progress) {
+        // The reference redraws a progress grid while its workers run (src/renderer.rs:300-365).  The trace kernel
+        // publishes its work-queue head in mapped host memory (an async device->host copy of the counter does not
+        // complete while the persistent kernel runs, measured), so the poll is a plain host read.
+        const unsigned long long total = ctx->items_total;
+        unsigned long long seen = 0;
+        auto last = std::chrono::steady_clock::now();
+        for (;;) {
+            cudaError_t q = cudaEventQuery(ctx->ev[1]);
+            if (q == cudaSuccess) break;
+            if (q != cudaErrorNotReady) { CU_TRY(q); }
+            std::this_thread::sleep_for(std::chrono::microseconds(500));   // the end of the kernel is noticed within 0.5 ms
+            auto now = std::chrono::steady_clock::now();
+            if (std::chrono::duration<double, std::milli>(now - last).count() < (double)ctx->progress_interval_ms) continue;
+            last = now;
+            unsigned long long claimed = *reinterpret_cast<volatile unsigned long long*>(ctx->h_progress);   // items handed out so far
+            if (claimed > total) claimed = total;                // the queue head runs past the end
+            if (claimed < seen) claimed = seen;                  // warps publish out of order
+            seen = claimed;
+            ctx->progress_cb(ctx->progress_user, claimed, total, std::chrono::duration<double>(now - t0).count());
+        }
+        ctx->progress_cb(ctx->progress_user, total, total, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    }
     rc = launch_resolve(ctx, ctx->d_accum, (long long)n_pix, params->samples_per_pixel, ctx->d_rgb8, st);
     if (rc) return rc;
     CU_TRY(cudaEventRecord(ctx->ev[2], st));
@@ -651,6 +685,23 @@ int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
 }
 
 int64_t rtb200_launch_count(rtb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int rtb200_set_progress(rtb200_ctx* ctx, rtb200_progress_fn fn, void* user, int32_t interval_ms) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "null context");
+    if (interval_ms < 1) interval_ms = 1;
+    if (fn) {   // created here, not inside rtb200_render: creating a stream or pinned memory waits for running kernels
+        CU_TRY(cudaSetDevice(ctx->device));
+        if (!ctx->h_progress) {
+            CU_TRY(cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_progress), sizeof(unsigned long long), cudaHostAllocMapped));
+            *ctx->h_progress = 0ull;
+            CU_TRY(cudaHostGetDevicePointer(reinterpret_cast<void**>(&ctx->d_progress), ctx->h_progress, 0));
+        }
+    }
+    ctx->progress_cb = fn;
+    ctx->progress_user = user;
+    ctx->progress_interval_ms = interval_ms;
+    return RTB200_OK;
+}
 
 int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "null context");

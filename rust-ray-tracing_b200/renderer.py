@@ -101,6 +101,18 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_fp32_peak(self._ctx, int(iters), C.byref(tf), C.byref(ms)))
         return tf.value, ms.value
 
+    def set_progress(self, callback=None, interval_ms: int = 100) -> None:
+        """callback(items_claimed, items_total, elapsed_seconds) is called from render() every interval_ms while the
+        trace kernel runs and once when it has finished (the reference's progress grid, src/renderer.rs:300-365, as a
+        callback).  None switches it off."""
+        if callback is None:
+            self._progress_c = None
+            _abi.check(_abi.lib.rtb200_set_progress(self._ctx, None, None, int(interval_ms)))
+            return
+        proto = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double)
+        self._progress_c = proto(lambda user, done, total, secs: callback(int(done), int(total), float(secs)))
+        _abi.check(_abi.lib.rtb200_set_progress(self._ctx, C.cast(self._progress_c, C.c_void_p), None, int(interval_ms)))
+
     def set_hit_mode(self, both_roots: bool) -> None:
         """False (default): the reference's packed path — near root only (src/objects.rs:272-276).
         True: the scalar Sphere::hit rule (src/objects.rs:227-234) — the far root when the near one is out of range,

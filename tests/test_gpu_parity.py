@@ -327,3 +327,24 @@ def test_both_roots_render_matches_oracle(rtb, renderer, oracle, scene_name, ray
     # and it is a different image from the reference's near-root-only rendering (glass refracts on the way out)
     img0, _ = renderer.render(50, spp, scene, rtb.Camera.default(W, H))
     assert not np.array_equal(img, img0)
+
+
+def test_progress_callback(rtb, renderer):
+    """rtb200_set_progress: monotone item counts ending at (total, total); the image is the one rendered without it."""
+    scene = rtb.scenes.random_spheres()
+    cam = rtb.Camera.default(640, 360)
+    renderer.seed = 9
+    ref, _ = renderer.render(50, 64, scene, cam)
+    calls = []
+    renderer.set_progress(lambda done, total, secs: calls.append((done, total, secs)), interval_ms=1)
+    try:
+        img, stat = renderer.render(50, 64, scene, cam)
+    finally:
+        renderer.set_progress(None)
+    assert np.array_equal(img, ref)
+    assert len(calls) >= 1 and calls[-1][0] == calls[-1][1] > 0
+    dones = [c[0] for c in calls]
+    assert dones == sorted(dones) and all(c[1] == calls[0][1] for c in calls) and all(c[2] >= 0 for c in calls)
+    n = len(calls)
+    renderer.render(50, 4, scene, cam)
+    assert len(calls) == n                                   # switched off again

@@ -245,3 +245,24 @@ def test_cli_renders_the_same_image_as_the_python_host(rtb, renderer, tmp_path):
     run([str(p), "-o", str(ppm), "--width", "160", "--height", "90", "--spp", "8", "--seed", "5", "--quiet"])
     body = open(ppm, "rb").read()
     assert body.startswith(b"P6\n160 90\n255\n") and np.array_equal(np.frombuffer(body[len(b"P6\n160 90\n255\n"):], np.uint8).reshape(90, 160, 3), img)
+
+
+@pytest.mark.gpu
+def test_cli_progress_and_both_roots(rtb, renderer, tmp_path):
+    """--progress draws on stderr without changing the image; --both-roots == the Python host with set_hit_mode(True)."""
+    scene = rtb.scenes.three_spheres()
+    p = tmp_path / "scene.toml"
+    p.write_text(scene.to_toml())
+    a, b = tmp_path / "a.png", tmp_path / "b.png"
+    r = run([str(p), "-o", str(a), "--width", "320", "--height", "180", "--spp", "32", "--seed", "3", "--quiet", "--progress"])
+    assert "100.0 %" in r.stderr and r.stdout.strip() == ""
+    renderer.seed = 3
+    img, _ = renderer.render(50, 32, scene, rtb.Camera.default(320, 180))
+    assert np.array_equal(read_png(a), img)
+    run([str(p), "-o", str(b), "--width", "320", "--height", "180", "--spp", "32", "--seed", "3", "--quiet", "--both-roots"])
+    renderer.set_hit_mode(True)
+    try:
+        img2, _ = renderer.render(50, 32, scene, rtb.Camera.default(320, 180))
+    finally:
+        renderer.set_hit_mode(False)
+    assert np.array_equal(read_png(b), img2) and not np.array_equal(img2, img)
