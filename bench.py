@@ -40,7 +40,11 @@ WORKLOADS = {
     "C4": ("ten_k_spheres", 1920, 1080, 64, 50),
     "C5": ("dielectric_heavy", 1920, 1080, 256, 50),
     "C1": ("three_spheres", 400, 225, 16, 50),
+    # fixed TOTAL sample counts, split over the GPUs (strong scaling): BASELINE configs[2] and the north_star target
+    "C3": ("random_spheres", 3840, 2160, 1000, 50),
+    "T": ("random_spheres", 1920, 1080, 1000, 50),
 }
+STRONG = {"C3", "T"}
 
 
 class ClockSampler:
@@ -175,7 +179,12 @@ def run_ours(args):
     gen, W, H, spp_per_gpu, depth = WORKLOADS[args.workload]
     if args.spp:
         spp_per_gpu = args.spp
-    spp_total = spp_per_gpu * world            # weak scaling: per-GPU work fixed
+    strong = args.workload in STRONG and not args.spp
+    if strong:
+        if spp_per_gpu % world:
+            raise SystemExit(f"{args.workload}: {spp_per_gpu} spp do not split over {world} GPUs")
+        spp_per_gpu //= world                  # strong scaling: total work fixed
+    spp_total = spp_per_gpu * world            # (weak scaling: per-GPU work fixed)
     scene = getattr(rtb.scenes, gen)()
     cam = rtb.Camera.default(W, H)
     renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays, stages=args.stages)
@@ -293,7 +302,7 @@ def run_ours(args):
     if rank == 0:
         line = {
             "metric": "Mpaths/s", "value": mpaths, "unit": "Mpaths/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {gen} {W}x{H}, {spp_per_gpu} spp per GPU ({spp_total} spp total), depth {depth}",
                        "n_spheres": n_spheres, "sharding": ("sample-range; exchange = " + {"p2p": "fused NVLink peer-memory reduce+resolve kernel (CUDA IPC), two 4-byte all-reduces as barriers",
