@@ -117,14 +117,23 @@ int validate_params(const rtb200_ctx* ctx, const rtb200_camera* cam, const rtb20
 }
 
 // Chooses log2 of the number of sample splits K (a power of two) so that the persistent grid has many more work items
-// than lanes (tail balance) while each item keeps at least 8 samples (register-resident sum).  RTB200_SPLITS_LOG2
-// overrides (tuning aid).
+// than lanes (tail balance) while each item keeps at least 16 samples: below that the per-item cost (claim, partial
+// plane write) shows — C2 at 100 spp: K = 1/2/4/8/16 take 58.4/51.3/45.8/47.5/47.4 ms (K = 1 loses a quarter to the tail
+// of the persistent grid; at 125, 256 and 1000 spp K = 4..16 are within 1 %; profiles/r1_splits_sweep.txt).  A variant
+// with shrinking phases in phase-major queue order (big items first, 8-sample items last) measured 4-10 % slower: its
+// phase-table lookups sit in the per-trip path.  RTB200_SPLITS_LOG2 overrides (tuning aid).
 int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
     if (const char* e = std::getenv("RTB200_SPLITS_LOG2")) { int v = std::atoi(e); if (v >= 0 && v <= 6) return v; }
-    long long lanes = (long long)ctx->prop.multiProcessorCount * 1024;
-    long long want_items = lanes * 64;
+    const long long slots = (long long)ctx->prop.multiProcessorCount * 2048;   // 1024 threads x 2 path slots per SM
     int lg = 0;
-    while (lg < 6 && (n_pix << lg) < want_items && (n_samples >> (lg + 1)) >= 8) lg++;
+    // (a) fill the machine: at least two items per path slot, down to 4 samples per item (small images: C1)
+    while (lg < 6 && (n_pix << lg) < 2 * slots && (n_samples >> (lg + 1)) >= 4) lg++;
+    // (b) tail balance: ~32 items per slot, while an item keeps enough work to amortise its claim and its partial-plane
+    //     write: 16 samples on a ~500-sphere scene, fewer where the sweeps are longer
+    const int n_sph = ctx->n_spheres > 0 ? ctx->n_spheres : 1;
+    int min_samples = (7776 + n_sph - 1) / n_sph;
+    min_samples = min_samples < 4 ? 4 : (min_samples > 16 ? 16 : min_samples);
+    while (lg < 6 && (n_pix << lg) < 32 * slots && (n_samples >> (lg + 1)) >= min_samples) lg++;
     return lg;
 }
 
