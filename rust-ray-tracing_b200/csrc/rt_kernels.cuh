@@ -461,6 +461,7 @@ struct TraceParams {
     uint32_t seed_lo, seed_hi;
     int sample_begin, sample_end; // global sample indices traced by this launch
     int row_begin, row_end;
+    int claim_chunk;              // work items a warp takes from the queue per atomic (1..64; slot_step)
     int both_roots;               // hit mode: 0 = near root only (the reference's packed path), 1 = scalar Sphere::hit rule
     int splits_log2;              // K = 1 << splits_log2: the sample range is cut into K contiguous sub-ranges, one work item each
     uint32_t width_magic;         // floor(2^32 / W) + 1 (0 when W == 1): row = pixel / W by multiply-high
@@ -562,8 +563,10 @@ __device__ __forceinline__ int split_sample(const TraceParams& P, const TraceCon
 //   2. write a finished item out and claim a new one (one atomic per warp);
 //   3. ONE Philox block: the next camera sample (Camera::get_ray) or this bounce's scatter
 //      (finalize + Material::get_hit_result).
+struct WarpChunk { uint32_t next = 0, end = 0; };   // the warp's private slice of the work queue (warp-uniform values)
+
 __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConsts& C, PathSlot& q, bool swept, float best_t, int best_i,
-                                          bool& exhausted, unsigned& n_segments, unsigned& n_paths, unsigned lane) {
+                                          bool& exhausted, WarpChunk& chunk, unsigned& n_segments, unsigned& n_paths, unsigned lane) {
     // ---- 1. terminate (src/ray_tracing.rs:353-357, :365-370) ----
     if (swept && q.has_path) {
         n_segments++;
@@ -590,19 +593,33 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     }
     const unsigned need_mask = __ballot_sync(0xffffffffu, q.item == NO_ITEM && !exhausted);
     if (need_mask) {
-        unsigned long long base64 = 0;
-        if (lane == 0) {
-            const unsigned long long n_claim = (unsigned long long)__popc(need_mask);
-            base64 = atomicAdd(P.work_counter, n_claim);
-            // progress for the host (rtb200_set_progress): every 4096 items the new queue head goes to mapped host memory
-            if (P.progress && ((base64 ^ (base64 + n_claim)) >> 12)) *reinterpret_cast<volatile unsigned long long*>(P.progress) = base64 + n_claim;
+        // The warp takes P.claim_chunk consecutive items from the global queue at a time and hands them to its lanes as
+        // they fall free (chunk.next/end are warp-uniform): one atomic per chunk, and the lanes of a warp keep working
+        // on neighbouring pixels, whose coherent rays keep the sweep's refine walks and the shading branches in step.
+        uint32_t avail = chunk.end - chunk.next;
+        if (avail == 0u) {
+            unsigned long long base64 = 0;
+            if (lane == 0) {
+                base64 = atomicAdd(P.work_counter, (unsigned long long)P.claim_chunk);
+                // progress for the host (rtb200_set_progress): every 4096 items the new queue head goes to mapped host memory
+                if (P.progress && ((base64 ^ (base64 + P.claim_chunk)) >> 12))
+                    *reinterpret_cast<volatile unsigned long long*>(P.progress) = base64 + P.claim_chunk;
+            }
+            base64 = __shfl_sync(0xffffffffu, base64, 0);
+            // n_items < 2^32 - 65536: a saturated head stays beyond the end
+            const uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;
+            if (base < C.n_items) {
+                chunk.next = base;
+                chunk.end = C.n_items - base < (uint32_t)P.claim_chunk ? C.n_items : base + (uint32_t)P.claim_chunk;
+            } else {
+                exhausted = true;                      // the queue is empty: warp-uniform
+            }
+            avail = chunk.end - chunk.next;
         }
-        base64 = __shfl_sync(0xffffffffu, base64, 0);
-        // items beyond n_items (< 2^32) saturate: the queue head only ever overshoots by the number of lanes
-        const uint32_t base = base64 > 0xffffffffull ? 0xffffffffu : (uint32_t)base64;
         if (q.item == NO_ITEM && !exhausted) {
-            const uint32_t item = base + __popc(need_mask & ((1u << lane) - 1u));
-            if (item >= base && item < C.n_items) {    // item = pixel * K + split: a warp works on neighbouring pixels
+            const uint32_t rank = __popc(need_mask & ((1u << lane) - 1u));
+            if (rank < avail) {                        // item = pixel * K + split (lanes beyond `avail` claim next trip)
+                const uint32_t item = chunk.next + rank;
                 q.item = item;
                 q.s = split_sample(P, C, item & C.split_mask);
                 q.acc = mk3(0.f, 0.f, 0.f);
@@ -611,10 +628,10 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
                     n_paths += (unsigned)(s_end - q.s);
                     q.s = s_end;
                 }
-            } else {
-                exhausted = true;
             }
         }
+        const uint32_t n_need = (uint32_t)__popc(need_mask);
+        chunk.next += n_need < avail ? n_need : avail;
     }
     // ---- 3. one Philox block: the next camera sample, or this bounce's scatter ----
     bool regen = false;
@@ -680,6 +697,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
 #pragma unroll
     for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
     bool exhausted = false;
+    WarpChunk chunk;
     unsigned n_segments = 0, n_paths = 0;          // per-lane counts (a lane traces far fewer than 2^32 segments)
     float best_t[RAYS];
     int best_i[RAYS];
@@ -691,7 +709,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, n_segments, n_paths, lane);
+            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -767,6 +785,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
         W(12, r) = NO_ITEM;
     }
     bool exhausted = false;
+    WarpChunk chunk;
     unsigned n_segments = 0, n_paths = 0;
     bool swept = false;
 
@@ -780,7 +799,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             q.item = W(12, r); q.s = (int)W(13, r);
             const uint32_t bw = W(14, r);
             q.bounce = (int)(bw & 0x7fffffffu); q.has_path = (bw >> 31) != 0u;
-            slot_step(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, n_segments, n_paths, lane);
+            slot_step(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, chunk, n_segments, n_paths, lane);
             W(0, r) = __float_as_uint(q.o.x); W(1, r) = __float_as_uint(q.o.y); W(2, r) = __float_as_uint(q.o.z);
             W(3, r) = __float_as_uint(q.d.x); W(4, r) = __float_as_uint(q.d.y); W(5, r) = __float_as_uint(q.d.z);
             W(6, r) = __float_as_uint(q.thr.x); W(7, r) = __float_as_uint(q.thr.y); W(8, r) = __float_as_uint(q.thr.z);

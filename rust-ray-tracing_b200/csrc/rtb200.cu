@@ -116,24 +116,22 @@ int validate_params(const rtb200_ctx* ctx, const rtb200_camera* cam, const rtb20
     return RTB200_OK;
 }
 
-// Chooses log2 of the number of sample splits K (a power of two) so that the persistent grid has many more work items
-// than lanes (tail balance) while each item keeps at least 16 samples: below that the per-item cost (claim, partial
-// plane write) shows — C2 at 100 spp: K = 1/2/4/8/16 take 58.4/51.3/45.8/47.5/47.4 ms (K = 1 loses a quarter to the tail
-// of the persistent grid; at 125, 256 and 1000 spp K = 4..16 are within 1 %; profiles/r1_splits_sweep.txt).  A variant
-// with shrinking phases in phase-major queue order (big items first, 8-sample items last) measured 4-10 % slower: its
-// phase-table lookups sit in the per-trip path.  RTB200_SPLITS_LOG2 overrides (tuning aid).
+// Chooses log2 of the number of sample splits K (a power of two): the persistent grid wants many more work items than
+// path slots (tail balance) while an item keeps enough samples to amortise its claim and its partial-plane write.
+// Measured on C2 with the chunked claims of slot_step (profiles/r1_splits_sweep.txt): 100 spp K = 2/4/8/16/32 take
+// 49.7/45.0/44.7/44.8/46.0 ms, 1000 spp K = 4/8/16/32: 444/434/433/432 ms.  RTB200_SPLITS_LOG2 overrides (tuning aid).
 int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
     if (const char* e = std::getenv("RTB200_SPLITS_LOG2")) { int v = std::atoi(e); if (v >= 0 && v <= 6) return v; }
     const long long slots = (long long)ctx->prop.multiProcessorCount * 2048;   // 1024 threads x 2 path slots per SM
     int lg = 0;
     // (a) fill the machine: at least two items per path slot, down to 4 samples per item (small images: C1)
     while (lg < 6 && (n_pix << lg) < 2 * slots && (n_samples >> (lg + 1)) >= 4) lg++;
-    // (b) tail balance: ~32 items per slot, while an item keeps enough work to amortise its claim and its partial-plane
-    //     write: 16 samples on a ~500-sphere scene, fewer where the sweeps are longer
+    // (b) tail balance: ~64 items per slot while an item keeps at least 6 samples on a ~500-sphere scene, fewer where
+    //     the sweeps are longer
     const int n_sph = ctx->n_spheres > 0 ? ctx->n_spheres : 1;
-    int min_samples = (7776 + n_sph - 1) / n_sph;
-    min_samples = min_samples < 4 ? 4 : (min_samples > 16 ? 16 : min_samples);
-    while (lg < 6 && (n_pix << lg) < 32 * slots && (n_samples >> (lg + 1)) >= min_samples) lg++;
+    int min_samples = (2916 + n_sph - 1) / n_sph;
+    min_samples = min_samples < 2 ? 2 : (min_samples > 6 ? 6 : min_samples);
+    while (lg < 6 && (n_pix << lg) < 64 * slots && (n_samples >> (lg + 1)) >= min_samples) lg++;
     return lg;
 }
 
@@ -155,6 +153,16 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     P.splits_log2 = choose_splits_log2(ctx, n_pix, n_samples);
     const int splits = 1 << P.splits_log2;
     P.width_magic = W > 1 ? (uint32_t)((1ull << 32) / (unsigned long long)W) + 1u : 0u;
+    {   // claim chunk: 64 items per warp and atomic on large launches (coherent lanes, measured best: 16/32/64/128/256 ->
+        // 45.7/44.8/44.9/45.5/47.8 ms on C2); smaller when the launch has fewer than ~4 chunks per warp (balance; C1:
+        // 1/2/4/8/16/64 -> 0.61/0.49/0.43/0.39/0.35/0.41 ms)
+        const long long warps = (long long)ctx->prop.multiProcessorCount * 32;
+        long long c = ((long long)n_pix * splits) / (warps * 4);
+        int chunk = 1;
+        while (chunk < 64 && chunk * 2 <= c) chunk *= 2;
+        if (const char* e = std::getenv("RTB200_CLAIM_CHUNK")) { int v = std::atoi(e); if (v >= 1 && v <= 4096) chunk = v; }
+        P.claim_chunk = chunk;
+    }
     P.work_counter = ctx->d_counters + 2;
     P.progress = (ctx->progress_cb && ctx->h_progress) ? ctx->d_progress : nullptr;
     if (ctx->h_progress) *ctx->h_progress = 0ull;
