@@ -348,3 +348,29 @@ def test_progress_callback(rtb, renderer):
     n = len(calls)
     renderer.render(50, 4, scene, cam)
     assert len(calls) == n                                   # switched off again
+
+
+@pytest.mark.parametrize("rays,stages", VARIANTS)
+def test_render_edge_shapes(rtb, renderer, oracle, rays, stages):
+    """Ragged and degenerate launches: empty scene, one-pixel and one-column images, sample counts that do not divide
+    into the kernel's work items, a sample sub-range that starts in the middle."""
+    S, M = rtb.Sphere, rtb.Material
+    renderer.rays_per_lane = rays
+    renderer.stages = stages
+    try:
+        empty = rtb.Scene.from_list([], {})
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, empty, 64, 36, 3, 50)
+        assert np.array_equal(img, ref_rgb) and stat.segments == ref_seg == 64 * 36 * 3 and stat.sphere_tests == 0
+        scene = rtb.scenes.three_spheres()
+        for W, H, spp in ((1, 1, 257), (1, 40, 7), (40, 1, 1), (33, 17, 13)):
+            cam = rtb.Camera(W, H, 10.0, 30.0, (16.0, 2.0, 18.5), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 0.0)
+            img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50, camera=cam)
+            assert stat.paths == W * H * spp and stat.segments == ref_seg
+            assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
+            assert np.array_equal(img, ref_rgb) and np.all(lin[..., 3] == spp)
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 48, 27, 20, 50, sample_range=(5, 12))
+        assert stat.paths == 48 * 27 * 7 and stat.segments == ref_seg and np.all(lin[..., 3] == 7)
+        assert np.abs(lin[..., :3].astype(np.float64) - ref_sum).max() <= 1e-4 * 7
+    finally:
+        renderer.rays_per_lane = 0
+        renderer.stages = 0
