@@ -374,3 +374,45 @@ def test_render_edge_shapes(rtb, renderer, oracle, rays, stages):
     finally:
         renderer.rays_per_lane = 0
         renderer.stages = 0
+
+
+def _wild_scene(rtb, n, seed):
+    """Spheres of very different sizes (radius 0.01 .. 10) scattered in a 40-unit cube, overlapping freely, all three
+    materials: nothing like the grid scenes the stage-1 axis choice and flooring were tuned on."""
+    rng = np.random.default_rng(seed)
+    S, M = rtb.Sphere, rtb.Material
+    mats = {"d": M.lambertian((0.7, 0.3, 0.3)), "m": M.metal((0.8, 0.8, 0.9), 0.05), "g": M.dielectric(1.5, False), "h": M.dielectric(1.3, True)}
+    names = list(mats)
+    objs = []
+    for i in range(n):
+        r = float(10.0 ** rng.uniform(-2.0, 1.0))
+        c = rng.uniform(-20.0, 20.0, size=3)
+        objs.append(S((float(c[0]), float(c[1]), float(c[2])), r, names[i % 4]))
+    return rtb.Scene.from_list(objs, mats)
+
+
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0)])
+@pytest.mark.parametrize("n,seed", [(300, 1), (900, 2), (3000, 3)])
+def test_render_wild_scene_matches_oracle(rtb, renderer, oracle, n, seed, rays, stages):
+    scene = _wild_scene(rtb, n, seed)
+    cam = rtb.Camera(96, 54, 10.0, 50.0, (45.0, 12.0, 50.0), (0.0, 0.0, 0.0), (0.0, 1.0, 0.0), 0.0)
+    renderer.rays_per_lane = rays
+    renderer.stages = stages
+    try:
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, 96, 54, 4, 12, camera=cam)
+    finally:
+        renderer.rays_per_lane = 0
+        renderer.stages = 0
+    assert stat.segments == ref_seg
+    assert np.abs(lin[..., :3].astype(np.float64) / 4 - ref_sum / 4).max() <= 1e-4
+    assert np.array_equal(img, ref_rgb)
+    assert (stat.segments > stat.paths * 1.2)                # the camera actually looks at the cloud
+
+
+def test_intersect_wild_scene(rtb, renderer, oracle):
+    scene = _wild_scene(rtb, 2000, 7)
+    rng = np.random.default_rng(5)
+    o = rng.uniform(-30, 30, size=(20000, 3)).astype(np.float32)
+    d = (rng.uniform(-20, 20, size=(20000, 3)) - o).astype(np.float32) * rng.uniform(0.01, 3.0, size=(20000, 1)).astype(np.float32)
+    idx, _ = _check_intersect(renderer, oracle, scene, o, d)
+    assert (idx >= 0).mean() > 0.5
