@@ -310,26 +310,32 @@ struct alignas(32) SpherePair { float4 filter, exact; };   // what stages 2 and 
 #define RTB_REFINE_INLINE __forceinline__   // two inlined copies (one per ray of the lane) beat one out-of-line copy by 5 %
 #endif
 
+// Next stage-1 candidate of the walk, in sweep order (false: none left).  The block index comes from the per-lane bitmap.
+__device__ __forceinline__ bool walk_next(const uint32_t* masks_r, int stride, uint32_t& todo, uint32_t& cand, int& last, int first_sphere,
+                                          int& idx) {
+    if (cand == 0u) {
+        if (todo == 0u) return false;
+        const int b = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        cand = ~masks_r[b * stride];                       // not empty: stage 1 set the block's bit
+        last = first_sphere + b * SWEEP_BLOCK + (SWEEP_BLOCK - 1);
+    }
+    uint32_t hi, bit;                                      // sphere j of the block sits at bit 31 - j: highest bit first
+    asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));       // FLO / BMSK: ptxas otherwise rebuilds clz and 0x80000000 >> clz
+    asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
+    cand ^= bit;
+    idx = last - (int)hi;
+    return true;
+}
+
 __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
                                           const SpherePair* __restrict__ g_pairs, FilterRay f, ExactRay ray, Best best) {
     if (todo == 0u) return best;
     const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                          // src/objects.rs:253
     const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
     uint32_t cand = 0;
-    int last = 0;                                          // index of the block's sphere 31
-    for (;;) {
-        if (cand == 0u) {
-            if (todo == 0u) break;
-            const int b = __ffs(todo) - 1;
-            todo &= todo - 1u;
-            cand = ~masks_r[b * stride];                   // not empty: stage 1 set the block's bit
-            last = first_sphere + b * SWEEP_BLOCK + (SWEEP_BLOCK - 1);
-        }
-        uint32_t hi, bit;                                  // sphere j of the block sits at bit 31 - j: highest bit first
-        asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));   // FLO / BMSK: ptxas otherwise rebuilds clz and 0x80000000 >> clz
-        asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
-        cand ^= bit;
-        const int idx = last - (int)hi;
+    int last = 0, idx = 0;                                 // last = index of the current block's sphere 31
+    while (walk_next(masks_r, stride, todo, cand, last, first_sphere, idx)) {
         const SpherePair* rec = g_pairs + idx;             // {filter, exact} of sphere idx
         const float4 fs = __ldg(&rec->filter);
         const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2
