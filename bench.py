@@ -356,7 +356,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage")
+    ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2, 3], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage, 3 = two-stage with shared-memory path state")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()

@@ -741,6 +741,67 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     flush_counters(P, n_paths, n_segments, lane);
 }
 
+// K2, large scenes: two-stage sweep with the stage-1 triples staged in shared memory and the path state of the RAYS
+// slots in REGISTERS (one CTA per SM has registers to spare: 65536 / THREADS per thread), so that shared memory holds
+// only the triples and the stage-1 masks and THREADS can be larger than in the shared-state variant: more warps to hide
+// the refine walks, whose sphere records come from L2 here (the L1 is all but given to shared memory).
+// dynamic smem: 8 * RAYS * THREADS mask words + n_padded * 3 floats.
+template <int THREADS, int RAYS>
+__global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_constant__ TraceParamsL PV) {
+    const TraceParams& P = PV.b;
+    extern __shared__ float4 smem4[];
+    uint32_t* masks = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
+    float4* s_slab = smem4 + 8 * RAYS * THREADS / 4;
+    {
+        const int n4 = PV.n_padded * 3 / 4;
+        for (int i = threadIdx.x; i < n4; i += THREADS) s_slab[i] = __ldg(&PV.s1[i]);
+        __syncthreads();
+    }
+    const TraceConsts C = trace_consts(P);
+    const unsigned lane = threadIdx.x & 31u;
+    PathSlot slot[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
+    bool exhausted = false;
+    WarpChunk chunk;
+    unsigned n_segments = 0, n_paths = 0;
+    float best_t[RAYS];
+    int best_i[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) { best_t[r] = RTB_INF; best_i[r] = -1; }
+    bool swept = false;
+    for (;;) {
+        bool any_path = false, idle = true;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            any_path = any_path || slot[r].has_path;
+            idle = idle && slot[r].item == NO_ITEM;
+        }
+        if (!__any_sync(0xffffffffu, any_path)) {
+            if (__all_sync(0xffffffffu, idle && exhausted)) break;
+            swept = false;
+            continue;
+        }
+        ExactRay ray[RAYS];
+        FilterRay flt[RAYS];
+        SlabRay slab[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
+            flt[r] = make_filter(slot[r].o, slot[r].d);
+            slab[r] = make_slab_ray(slot[r].o.x, slot[r].o.y, slot[r].o.z, slot[r].d.x, slot[r].d.y, slot[r].d.z, plen2_3(slot[r].d), PV.up_axis,
+                                    PV.rp_min);
+            best_t[r] = RTB_INF;
+            best_i[r] = -1;
+        }
+        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, masks, THREADS, slab,
+                              flt, best_t, best_i);
+        swept = true;
+    }
+    flush_counters(P, n_paths, n_segments, lane);
+}
+
 // K2, parameter-space variant (scenes of at most N spheres): the filter spheres are kernel parameters, so the sweep's
 // sphere operand sits in uniform registers, and every lane runs RAYS path slots whose state lives in SHARED memory
 // between trips (word w of slot r of thread t at st[(w * RAYS + r) * THREADS + t]: conflict-free).  The shading step

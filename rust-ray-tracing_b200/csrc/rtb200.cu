@@ -14,6 +14,10 @@
 #include <thread>
 #include <vector>
 
+#ifndef RTB_LR_THREADS
+#define RTB_LR_THREADS 640
+#endif
+
 namespace {
 
 thread_local std::string g_last_error;
@@ -198,6 +202,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto k_s2560 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS2560>;
     constexpr int LT = 512;                            // shared-memory two-stage variant: one 512-thread CTA per SM
     auto k_sl = rtb::k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL>;
+    constexpr int LRT = RTB_LR_THREADS;                // register-state variant of the same
+    auto k_slr = rtb::k_trace_paths_l<LRT, VR>;
     auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
     auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
     if (!ctx->attrs_set) {
@@ -206,6 +212,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         CU_TRY(cudaFuncSetAttribute(k_s512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_s2560, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_sl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_slr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
@@ -243,7 +250,9 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
-        k_sl<<<sms, LT, smem_sl, st>>>(pl);
+        const size_t smem_slr = (size_t)8 * VR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
+        if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) k_slr<<<sms, LRT, smem_slr, st>>>(pl);
+        else k_sl<<<sms, LT, smem_sl, st>>>(pl);
     } else if (use_v && P.n_spheres <= 512) {
         auto* pv = reinterpret_cast<PV512*>(ctx->h_params.data());
         pv->b = P;

@@ -201,6 +201,42 @@ def test_full_size_properties(rtb, renderer):
     assert img.shape == (H, W, 3) and img.dtype == np.uint8
 
 
+FULL_SIZE = [("three_spheres", 400, 225, 16, [(1, 0), (2, 1), (2, 2)]),            # C1 in full
+             ("random_spheres", 1920, 1080, 4, [(1, 0), (2, 1), (2, 2)]),           # C2 / T geometry
+             ("dielectric_heavy", 1920, 1080, 4, [(1, 0), (2, 1), (2, 2)]),         # C5 geometry
+             ("ten_k_spheres", 1920, 1080, 2, [(1, 0), (2, 1), (2, 3)])]            # C4 geometry
+
+
+@pytest.mark.parametrize("scene_name,W,H,spp,variants", FULL_SIZE)
+def test_full_size_strips_match_oracle_and_variants_agree(rtb, renderer, oracle, scene_name, W, H, spp, variants):
+    """BASELINE configs at their full resolution (reduced spp, so the oracle finishes in seconds): (1) nine horizontal strips
+    of the image (top to bottom, three rows each) are bit-compared with oracle<float> rendering the same rows of the same
+    full-size job; (2) every kernel variant renders the whole frame to the identical linear image, RGB8 image and
+    segment count as the library's own choice — so the strips vouch for whichever kernel runs."""
+    scene = getattr(rtb.scenes, scene_name)()
+    cam = rtb.Camera.default(W, H)
+    renderer.seed = 1
+    img, lin, stat = renderer.render(50, spp, scene, cam, want_linear=True)
+    assert stat.paths == W * H * spp and np.all(lin[..., 3] == spp)
+    strips = [(int(r), int(r) + 3) for r in np.linspace(0, H - 3, 9)]
+    for r0, r1 in strips:
+        ref_sum, ref_rgb, _ = oracle.render(scene.arrays(), W, H, cam.vectors(), spp, 50, seed=1, f32=True, row_range=(r0, r1))
+        err = np.abs(lin[r0:r1, :, :3].astype(np.float64) / spp - ref_sum[r0:r1] / spp).max()
+        assert err <= 1e-4, (r0, err)
+        assert np.array_equal(img[r0:r1], ref_rgb[r0:r1]), (r0, r1)
+    for rays, stages in variants:
+        renderer.rays_per_lane = rays
+        renderer.stages = stages
+        try:
+            img_v, lin_v, stat_v = renderer.render(50, spp, scene, cam, want_linear=True)
+        finally:
+            renderer.rays_per_lane = 0
+            renderer.stages = 0
+        assert stat_v.segments == stat.segments, (rays, stages)
+        assert np.array_equal(lin_v, lin), (rays, stages)
+        assert np.array_equal(img_v, img), (rays, stages)
+
+
 def test_errors_are_reported_not_fatal(rtb, renderer):
     scene = rtb.scenes.three_spheres()
     cam = rtb.Camera.default(16, 9)
@@ -261,11 +297,11 @@ def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays, stages):
     assert np.array_equal(img, ref_rgb)
 
 
-@pytest.mark.parametrize("rays,stages", VARIANTS)
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 3)])
 @pytest.mark.parametrize("half", [28, 50])
 def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, stages):
-    """Scenes beyond the parameter-space capacity (3 137 and 10 001 spheres): the shared-memory two-stage variant
-    (default), the resident one-stage variant (stages=1) and the one-ray resident variant against the oracle."""
+    """Scenes beyond the parameter-space capacity (3 137 and 10 001 spheres): the shared-memory two-stage variant with
+    the path state in registers (default) and in shared memory (stages=3), the resident one-stage variant (stages=1) and the one-ray resident variant against the oracle."""
     scene = rtb.scenes._grid_scene(half, 77 + half, 0.6, 0.25, big=False)
     W, H, spp = 96, 54, 2
     renderer.rays_per_lane = rays
@@ -391,7 +427,7 @@ def _wild_scene(rtb, n, seed):
     return rtb.Scene.from_list(objs, mats)
 
 
-@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0)])
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0), (2, 3)])
 @pytest.mark.parametrize("n,seed", [(300, 1), (900, 2), (3000, 3)])
 def test_render_wild_scene_matches_oracle(rtb, renderer, oracle, n, seed, rays, stages):
     scene = _wild_scene(rtb, n, seed)
