@@ -388,7 +388,10 @@ struct SmemSlab {
 template <int RAYS, class S1, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const SpherePair* __restrict__ g_pairs, int count,
                                                 uint32_t* masks, int stride,
-                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS],
+                                                int base_block = 0) {
+    // `count` spheres of the stage-1 source starting at its block 0; they are spheres base_block * 32 ... of the scene
+    // (base_block != 0: the tiled kernel, whose stage-1 source is one tile of the scene).
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
         const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
@@ -413,7 +416,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], (base_block + cb) * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -797,6 +800,77 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         }
         sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, masks, THREADS, slab,
                               flt, best_t, best_i);
+        swept = true;
+    }
+    flush_counters(P, n_paths, n_segments, lane);
+}
+
+// K2, scenes of any size: the sweep of k_trace_paths_l with the stage-1 triples streamed through shared memory in
+// TILES.  The warps of a CTA run their loop trips in lockstep (one CTA-wide vote per trip, two barriers per tile): the
+// CTA loads a tile of triples, every warp runs stages 1-3 of its 2 x 32 rays against it, then the next tile replaces
+// it.  A tile sweep is ~4.4 instructions x tile_spheres x RAYS per warp (>= 10^5 issue slots for the 15 000-sphere
+// tile), so neither the barriers nor the reload (12 B per sphere, L2-resident, once per trip) weigh anything.
+// Candidates are still visited in list order across tiles, so the `<=` tie-break (last object wins) is unchanged.
+// dynamic smem: 8 * RAYS * THREADS mask words + tile_spheres * 3 floats.  tile_spheres is a multiple of 32.
+template <int THREADS, int MIN_BLOCKS, int RAYS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_t(const __grid_constant__ TraceParamsL PV, const int tile_spheres) {
+    const TraceParams& P = PV.b;
+    extern __shared__ float4 smem4[];
+    uint32_t* masks = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
+    float4* s_slab = smem4 + 8 * RAYS * THREADS / 4;
+    const TraceConsts C = trace_consts(P);
+    const unsigned lane = threadIdx.x & 31u;
+    PathSlot slot[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
+    bool exhausted = false;
+    WarpChunk chunk;
+    unsigned n_segments = 0, n_paths = 0;
+    float best_t[RAYS];
+    int best_i[RAYS];
+#pragma unroll
+    for (int r = 0; r < RAYS; r++) { best_t[r] = RTB_INF; best_i[r] = -1; }
+    bool swept = false;
+    for (;;) {
+        bool any_path = false, idle = true;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            any_path = any_path || slot[r].has_path;
+            idle = idle && slot[r].item == NO_ITEM;
+        }
+        const bool warp_sweeps = __any_sync(0xffffffffu, any_path);
+        // CTA-wide vote; as a barrier it also says that every warp is done with the previous trip's last tile
+        if (!__syncthreads_or(any_path ? 1 : 0)) {
+            if (__syncthreads_and((idle && exhausted) ? 1 : 0)) break;
+            swept = false;
+            continue;
+        }
+        ExactRay ray[RAYS];
+        FilterRay flt[RAYS];
+        SlabRay slab[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
+            flt[r] = make_filter(slot[r].o, slot[r].d);
+            slab[r] = make_slab_ray(slot[r].o.x, slot[r].o.y, slot[r].o.z, slot[r].d.x, slot[r].d.y, slot[r].d.z, plen2_3(slot[r].d), PV.up_axis,
+                                    PV.rp_min);
+            best_t[r] = RTB_INF;
+            best_i[r] = -1;
+        }
+        for (int t0 = 0; t0 < PV.n_padded; t0 += tile_spheres) {
+            const int cnt = PV.n_padded - t0 < tile_spheres ? PV.n_padded - t0 : tile_spheres;
+            if (t0 > 0) __syncthreads();                       // every warp is done with the previous tile
+            {
+                const float4* src = PV.s1 + (size_t)t0 * 3 / 4;
+                const int n4 = cnt * 3 / 4;
+                for (int i = threadIdx.x; i < n4; i += THREADS) s_slab[i] = __ldg(&src[i]);
+            }
+            __syncthreads();
+            if (warp_sweeps)                                   // a warp without a live path only keeps the barriers
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), cnt, masks, THREADS, slab,
+                                      flt, best_t, best_i, t0 / SWEEP_BLOCK);
+        }
         swept = true;
     }
     flush_counters(P, n_paths, n_segments, lane);

@@ -51,7 +51,8 @@ class CudaRenderer(Renderer):
     def __init__(self, device: int = 0, seed: int = 1, rays_per_lane: int = 0, stages: int = 0):
         """rays_per_lane: 0 = the library's default trace kernel, 1 / 2 = force that variant (RTB200_FLAG_RAYS1/2).
         stages: 0 = the library decides, 1 / 2 = force the one- / two-stage sweep (RTB200_FLAG_ONE_STAGE / _TWO_STAGE),
-        3 = two-stage with the path state in shared memory (adds RTB200_FLAG_SHARED_STATE; matters beyond 2560 spheres)."""
+        3 = two-stage with the path state in shared memory (adds RTB200_FLAG_SHARED_STATE; matters beyond 2560 spheres),
+        4 = the tiled two-stage kernel (RTB200_FLAG_TILED: what scenes beyond ~10 600 spheres get)."""
         self.rays_per_lane = int(rays_per_lane)
         self.stages = int(stages)
         self._ctx = C.c_void_p()
@@ -131,7 +132,7 @@ class CudaRenderer(Renderer):
     def _params(self, max_bounces, spp, camera, sample_range, row_range) -> _abi.Params:
         s0, s1 = sample_range if sample_range is not None else (0, spp)
         r0, r1 = row_range if row_range is not None else (0, camera.image_height())
-        flags = {0: 0, 1: 1, 2: 2}[self.rays_per_lane] | {0: 0, 1: 4, 2: 8, 3: 8 | 32}[self.stages]
+        flags = {0: 0, 1: 1, 2: 2}[self.rays_per_lane] | {0: 0, 1: 4, 2: 8, 3: 8 | 32, 4: 64}[self.stages]
         return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), flags, 0)
 
     # ---- Renderer::render -------------------------------------------------------------------------------------

@@ -69,6 +69,12 @@ def ten_k_spheres(seed: int = 20240608) -> Scene:
     return _grid_scene(50, seed, 0.80, 0.15, big=False)
 
 
+def forty_k_spheres(seed: int = 20240610) -> Scene:
+    """Beyond the BASELINE configs: 200x200 jittered grid + ground = 40 001 spheres, the scene size at which the stage-1
+    data no longer fit in shared memory at once (three tiles of the tiled trace kernel)."""
+    return _grid_scene(100, seed, 0.80, 0.15, big=False)
+
+
 def dielectric_heavy(seed: int = 20240609) -> Scene:
     """S4 (config C5): S2 layout with 10 % lambertian / 10 % metal / 80 % dielectric."""
     return _grid_scene(11, seed, 0.10, 0.10)

@@ -1,0 +1,127 @@
+"""The committed fixtures under tests/golden/ (written by tests/golden/make_golden.py from the CPU oracle; the reference
+has no fixtures of its own for this path).
+
+CPU: the oracle built here reproduces them bit for bit (it cannot drift silently) and every host loads the TOML fixture
+into the stored scene arrays.  GPU (-m gpu): the CUDA path, through the C ABI, reproduces the files written on another
+machine — hit/miss and index exact, t within 1e-5 relative (bit-equal in practice), images within 1e-4 per channel before
+quantisation (BASELINE.json), RGB8 identical."""
+import os
+
+import numpy as np
+import pytest
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RENDERS = ["three_spheres", "random_spheres", "dielectric_heavy", "depth3"]
+GENERATOR = {"three_spheres": "three_spheres", "random_spheres": "random_spheres", "dielectric_heavy": "dielectric_heavy",
+             "depth3": "random_spheres"}
+
+
+def _load(name):
+    return np.load(os.path.join(GOLDEN, name))
+
+
+def _arrays(g):
+    return tuple(g[k] for k in ("spheres", "mat_index", "kind", "hollow", "albedo", "param"))
+
+
+@pytest.mark.parametrize("name", RENDERS)
+def test_scene_generators_reproduce_the_stored_scenes(rtb, name):
+    g = _load(f"render_{name}.npz")
+    scene = getattr(rtb.scenes, GENERATOR[name])()
+    for a, b in zip(scene.arrays(), _arrays(g)):
+        assert np.array_equal(np.asarray(a), b)
+    cam = rtb.Camera.default(int(g["W"]), int(g["H"]))
+    assert np.array_equal(np.asarray(cam.vectors(), dtype=np.float64), g["cam18"])
+
+
+@pytest.mark.parametrize("tag", ["f32", "f64"])
+@pytest.mark.parametrize("name", RENDERS)
+def test_oracle_reproduces_golden_renders(oracle, name, tag):
+    g = _load(f"render_{name}.npz")
+    W, H, spp, depth, seed = (int(g[k]) for k in ("W", "H", "spp", "depth", "seed"))
+    s, rgb, seg = oracle.render(_arrays(g), W, H, g["cam18"], spp, depth, seed=seed, f32=(tag == "f32"))
+    assert seg == int(g["segments_" + tag])
+    assert np.array_equal(s, g["sum_" + tag])            # bit for bit, whatever the thread count
+    assert np.array_equal(rgb, g["rgb8_" + tag])
+
+
+@pytest.mark.parametrize("tag", ["f32", "f64"])
+def test_oracle_reproduces_golden_intersections(oracle, tag):
+    g = _load("intersect_random_spheres.npz")
+    idx, t = oracle.intersect(g["spheres"], g["rays"], enabled=g["enabled"], f32=(tag == "f32"))
+    assert np.array_equal(idx, g["idx_" + tag])
+    assert np.array_equal(t, g["t_" + tag])
+    assert np.all(idx[g["enabled"] == 0] == -1)           # a disabled lane never hits (src/objects.rs:259,277)
+
+
+def _f32_vs_f64(t, g):
+    hit = g["idx_f64"] >= 0
+    return np.abs(np.asarray(t, dtype=np.float64)[hit] - g["t_f64"][hit]) / np.abs(g["t_f64"][hit])
+
+
+def test_f32_golden_against_f64_golden():
+    """What FP32 (the north_star's arithmetic) costs against the reference's f64 on the stored batch: hit/miss and index
+    are the same for all 4096 rays; t agrees to a median of 1.3e-6 relative, but the reference-order discriminant
+    (src/objects.rs:252-257) cancels in f32 — 1000-unit ground sphere, grazing hits from 13 units away — so only 77 % of
+    the hits are inside BASELINE's 1e-5 and the worst is 6e-4.  The 1e-5 bar is therefore asserted against oracle<float>
+    (same arithmetic, where the CUDA path is bit-equal) and these figures are asserted here as the f32-vs-f64 envelope."""
+    g = _load("intersect_random_spheres.npz")
+    assert np.array_equal(g["idx_f32"], g["idx_f64"])
+    rel = _f32_vs_f64(g["t_f32"], g)
+    assert np.median(rel) < 2e-6 and (rel <= 1e-5).mean() > 0.75 and rel.max() < 1e-3
+
+
+def test_toml_fixture_loads_into_the_stored_scene(rtb):
+    g = _load("render_three_spheres.npz")
+    scene = rtb.Scene.from_toml(open(os.path.join(GOLDEN, "three_spheres.toml")).read())
+    for a, b in zip(scene.arrays(), _arrays(g)):
+        assert np.array_equal(np.asarray(a), b)
+
+
+# ---- GPU -------------------------------------------------------------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("stages", [0, 1, 2, 4])
+@pytest.mark.parametrize("name", RENDERS)
+def test_cuda_render_matches_golden(rtb, renderer, name, stages):
+    g = _load(f"render_{name}.npz")
+    W, H, spp, depth, seed = (int(g[k]) for k in ("W", "H", "spp", "depth", "seed"))
+    scene = getattr(rtb.scenes, GENERATOR[name])()
+    cam = rtb.Camera.default(W, H)
+    renderer.seed = seed
+    renderer.stages = stages
+    try:
+        img, lin, stat = renderer.render(depth, spp, scene, cam, want_linear=True)
+    finally:
+        renderer.stages = 0
+        renderer.seed = 1
+    err = np.abs(lin[..., :3].astype(np.float64) / spp - g["sum_f32"] / spp).max()
+    assert err <= 1e-4, err                                # the bar; bit-identical up to the order of the partial sums
+    assert stat.segments == int(g["segments_f32"])
+    assert np.array_equal(img, g["rgb8_f32"])
+    # and against the reference-faithful f64 oracle: statistically the same image (silhouette samples may flip)
+    d64 = np.abs(lin[..., :3].astype(np.float64) / spp - g["sum_f64"] / spp)
+    assert np.median(d64) < 1e-5 and (d64.max(axis=2) > 1e-4).mean() < 0.05
+
+
+@pytest.mark.gpu
+def test_cuda_intersect_matches_golden(rtb, renderer):
+    g = _load("intersect_random_spheres.npz")
+    scene = rtb.scenes.random_spheres()
+    rays = g["rays"].astype(np.float32)
+    idx, t = renderer.intersect_batch(scene, rays[:, :3], rays[:, 3:], enabled=g["enabled"].astype(np.uint8))
+    assert np.array_equal(idx, g["idx_f32"])
+    hit = idx >= 0
+    assert np.array_equal(t[hit].astype(np.float64), g["t_f32"][hit])                       # bit-equal to oracle<float>
+    assert np.array_equal(idx, g["idx_f64"])                                                # against f64: same index for every ray,
+    rel = _f32_vs_f64(t, g)                                                                 # t inside the f32 envelope (see above)
+    assert np.median(rel) < 2e-6 and (rel <= 1e-5).mean() > 0.75 and rel.max() < 1e-3
+
+
+@pytest.mark.gpu
+def test_cuda_renders_the_toml_fixture(rtb, renderer):
+    g = _load("render_three_spheres.npz")
+    W, H, spp, depth, seed = (int(g[k]) for k in ("W", "H", "spp", "depth", "seed"))
+    scene = rtb.Scene.from_toml(open(os.path.join(GOLDEN, "three_spheres.toml")).read())
+    renderer.seed = seed
+    img, stat = renderer.render(depth, spp, scene, rtb.Camera.default(W, H))
+    assert np.array_equal(img, g["rgb8_f32"]) and stat.segments == int(g["segments_f32"])

@@ -204,7 +204,7 @@ def test_full_size_properties(rtb, renderer):
 FULL_SIZE = [("three_spheres", 400, 225, 16, [(1, 0), (2, 1), (2, 2)]),            # C1 in full
              ("random_spheres", 1920, 1080, 4, [(1, 0), (2, 1), (2, 2)]),           # C2 / T geometry
              ("dielectric_heavy", 1920, 1080, 4, [(1, 0), (2, 1), (2, 2)]),         # C5 geometry
-             ("ten_k_spheres", 1920, 1080, 2, [(1, 0), (2, 1), (2, 3)])]            # C4 geometry
+             ("ten_k_spheres", 1920, 1080, 2, [(1, 0), (2, 1), (2, 3), (2, 4)])]    # C4 geometry
 
 
 @pytest.mark.parametrize("scene_name,W,H,spp,variants", FULL_SIZE)
@@ -309,6 +309,56 @@ def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, st
     img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
     renderer.rays_per_lane = 0
     renderer.stages = 0
+    assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
+    assert stat.segments == ref_seg
+    assert stat.sphere_tests == ref_seg * len(scene)
+    assert np.array_equal(img, ref_rgb)
+
+
+@pytest.mark.parametrize("tile", [32, 96, 1024, 0])
+@pytest.mark.parametrize("scene_name,W,H,spp", [("three_spheres", 96, 54, 8), ("random_spheres", 96, 54, 4), ("tube", 96, 54, 4),
+                                                ("grid28", 64, 36, 2)])
+def test_tiled_kernel_matches_oracle(rtb, renderer, oracle, monkeypatch, scene_name, W, H, spp, tile):
+    """RTB200_FLAG_TILED (stages=4): the kernel scenes beyond ~10 600 spheres get, forced onto small scenes with tiles of
+    32 / 96 / 1024 spheres (RTB200_TILE_SPHERES) so that they cross many tile boundaries — ragged last tile, a one-tile
+    scene, candidates of one ray in several tiles (the tube) — and with the library's own tile size (0)."""
+    cam = None
+    if scene_name == "tube":
+        scene = _tube_scene(rtb, 700)
+        cam = rtb.Camera(W, H, 1.0, 40.0, (0.3, 0.2, 2.0), (0.0, 0.0, -10.0), (0.0, 1.0, 0.0), 0.0)
+    elif scene_name == "grid28":
+        scene = rtb.scenes._grid_scene(28, 105, 0.6, 0.25, big=False)
+    else:
+        scene = getattr(rtb.scenes, scene_name)()
+    if tile:
+        monkeypatch.setenv("RTB200_TILE_SPHERES", str(tile))
+    else:
+        monkeypatch.delenv("RTB200_TILE_SPHERES", raising=False)
+    renderer.stages = 4
+    try:
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50, camera=cam)
+    finally:
+        renderer.stages = 0
+    assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
+    assert stat.segments == ref_seg
+    assert np.array_equal(img, ref_rgb)
+
+
+@pytest.mark.parametrize("half,both_roots", [(55, False), (75, False), (75, True)])
+def test_render_scene_beyond_shared_memory_matches_oracle(rtb, renderer, oracle, half, both_roots):
+    """Scenes whose stage-1 data no longer fit in shared memory at once (12 101 and 22 501 spheres; the reference has no
+    limit on Vec<Object>, src/ray_tracing.rs:102-104): the library's own choice must be the tiled kernel (two tiles), and
+    the image, segment count and RGB8 output equal the oracle's."""
+    scene = rtb.scenes._grid_scene(half, 300 + half, 0.6, 0.25, big=False)
+    assert len(scene) == (2 * half) ** 2 + 1
+    W, H, spp = 128, 72, 2
+    renderer.set_hit_mode(both_roots)
+    oracle.set_both_roots(both_roots)
+    try:
+        img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50)
+    finally:
+        renderer.set_hit_mode(False)
+        oracle.set_both_roots(False)
     assert np.abs(lin[..., :3].astype(np.float64) / spp - ref_sum / spp).max() <= 1e-4
     assert stat.segments == ref_seg
     assert stat.sphere_tests == ref_seg * len(scene)
