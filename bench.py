@@ -40,7 +40,7 @@ WORKLOADS = {
     "C4": ("ten_k_spheres", 1920, 1080, 64, 50),
     "C5": ("dielectric_heavy", 1920, 1080, 256, 50),
     "C1": ("three_spheres", 400, 225, 16, 50),
-    # beyond BASELINE: 40 001 spheres, the tiled trace kernel (stage-1 data streamed through shared memory)
+    # beyond BASELINE: 40 001 spheres, the streamed trace kernel (stage-1 data fetched per warp from global memory)
     "L40K": ("forty_k_spheres", 1920, 1080, 16, 50),
     # fixed TOTAL sample counts, split over the GPUs (strong scaling): BASELINE configs[2] and the north_star target
     "C3": ("random_spheres", 3840, 2160, 1000, 50),
@@ -358,7 +358,7 @@ def main():
     ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2, 3, 4], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage, 3 = two-stage with shared-memory path state, 4 = tiled two-stage")
+    ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2, 3, 4], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage, 3 = two-stage with shared-memory path state, 4 = streamed two-stage (any scene size)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()

@@ -95,8 +95,9 @@ typedef struct rtb200_params {
 #define RTB200_FLAG_SHARED_STATE 32 /* scenes beyond 2560 spheres, two-stage sweep: keep the path state in shared memory (512
                                       threads per SM) instead of registers (640 threads per SM, the default)            */
 
-#define RTB200_FLAG_TILED 64 /* force the tiled two-stage kernel: stage-1 data streamed through shared memory in tiles, the
-                               kernel every scene beyond ~10 600 spheres gets (no upper limit on the scene size)        */
+#define RTB200_FLAG_STREAMED 64 /* force the streamed two-stage kernel: stage-1 data fetched per warp from global memory
+                                  (cp.async double buffer) — the kernel every scene beyond ~10 600 spheres gets; there is
+                                  no upper limit on the scene size, like the reference's Vec<Object>                    */
 
 #define RTB200_FLAG_BOTH_ROOTS 16 /* this call only: RTB200_HIT_BOTH_ROOTS (see rtb200_set_hit_mode) */
 

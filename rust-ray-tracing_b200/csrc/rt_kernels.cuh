@@ -388,10 +388,7 @@ struct SmemSlab {
 template <int RAYS, class S1, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const SpherePair* __restrict__ g_pairs, int count,
                                                 uint32_t* masks, int stride,
-                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS],
-                                                int base_block = 0) {
-    // `count` spheres of the stage-1 source starting at its block 0; they are spheres base_block * 32 ... of the scene
-    // (base_block != 0: the tiled kernel, whose stage-1 source is one tile of the scene).
+                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
         const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
@@ -416,11 +413,77 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], (base_block + cb) * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
     }
+}
+
+// The two-stage sweep with the stage-1 triples STREAMED from global memory (L2-resident) through a per-warp double
+// buffer: while the warp sweeps chunk c (8 blocks = 256 spheres = 3 KB of triples), `cp.async` brings chunk c + 1 into
+// the other half of its 6 KB buffer.  No CTA barrier and no CTA-wide staging, so the scene size is unbounded and the
+// warps of a CTA stay independent (the persistent loop's trips are not in lockstep).  A chunk sweep is ~2 250 issue
+// slots of this warp, i.e. >= 10^4 cycles with five warps per sub-partition: the L2 latency is hidden many times over,
+// and the fill traffic is 3 KB per chunk and warp (~5.5 B/clk/SM).
+__device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int STREAM_CHUNK_F4 = 8 * SWEEP_BLOCK * 3 / 4;     // float4 per chunk of 8 blocks: 192 (3 KB)
+
+template <int RAYS, class RaySrc>
+__device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float4* __restrict__ g_s1, unsigned lane, const RaySrc& rays,
+                                                       const SpherePair* __restrict__ g_pairs, int n_padded, uint32_t* masks, int stride,
+                                                       const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS],
+                                                       int (&best_i)[RAYS]) {
+    const int n_blocks = n_padded / SWEEP_BLOCK;              // the device arrays are padded to whole blocks
+    const int n_chunks = (n_blocks + 7) / 8;
+    auto issue = [&](int c) {                                 // chunk c -> half (c & 1) of the warp's buffer, one commit group
+        const int nb = n_blocks - c * 8 < 8 ? n_blocks - c * 8 : 8;
+        const float4* src = g_s1 + (size_t)c * STREAM_CHUNK_F4;
+        float4* dst = wbuf + (c & 1) * STREAM_CHUNK_F4;
+        for (int i = (int)lane; i < nb * (SWEEP_BLOCK * 3 / 4); i += 32) cp_async_16(dst + i, src + i);
+        cp_async_commit();
+    };
+    issue(0);
+    for (int c = 0; c < n_chunks; c++) {
+        if (c + 1 < n_chunks) issue(c + 1);
+        else cp_async_commit();                               // an empty group keeps "all but the newest" = chunk c
+        cp_async_wait<1>();
+        __syncwarp();                                         // every lane's part of chunk c has landed
+        const int nb = n_blocks - c * 8 < 8 ? n_blocks - c * 8 : 8;
+        const SmemSlab s1{wbuf + (c & 1) * STREAM_CHUNK_F4};
+        uint32_t todo[RAYS];
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) todo[r] = 0u;
+        uint32_t bit = 1u;
+#pragma unroll 1
+        for (int b = 0; b < nb; b++, bit <<= 1) {             // ---- stage 1 ----
+            uint32_t mask[RAYS];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = 0;
+            s1.template block<RAYS>(b, sl, mask);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                masks[(r * 8 + b) * stride] = mask[r];
+                todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
+            }
+        }
+        __syncwarp();                                         // all lanes are done reading this half before chunk c + 2 refills it
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
+            Best bst{best_t[r], best_i[r]};
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
+            best_t[r] = bst.t;
+            best_i[r] = bst.i;
+        }
+    }
+    cp_async_wait<0>();
 }
 
 // ---- K1 ----------------------------------------------------------------------------------------------------------
@@ -805,19 +868,18 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
     flush_counters(P, n_paths, n_segments, lane);
 }
 
-// K2, scenes of any size: the sweep of k_trace_paths_l with the stage-1 triples streamed through shared memory in
-// TILES.  The warps of a CTA run their loop trips in lockstep (one CTA-wide vote per trip, two barriers per tile): the
-// CTA loads a tile of triples, every warp runs stages 1-3 of its 2 x 32 rays against it, then the next tile replaces
-// it.  A tile sweep is ~4.4 instructions x tile_spheres x RAYS per warp (>= 10^5 issue slots for the 15 000-sphere
-// tile), so neither the barriers nor the reload (12 B per sphere, L2-resident, once per trip) weigh anything.
-// Candidates are still visited in list order across tiles, so the `<=` tie-break (last object wins) is unchanged.
-// dynamic smem: 8 * RAYS * THREADS mask words + tile_spheres * 3 floats.  tile_spheres is a multiple of 32.
-template <int THREADS, int MIN_BLOCKS, int RAYS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_t(const __grid_constant__ TraceParamsL PV, const int tile_spheres) {
+// K2, scenes of ANY size: k_trace_paths_l with the stage-1 triples streamed per warp from global memory
+// (sweep_two_stage_stream) instead of staged once per CTA: nothing of the scene has to fit in shared memory.  Path state
+// in registers, warps independent.  Measured against a CTA-lockstep variant that staged tiles of ~15 000 spheres per
+// CTA behind two barriers per tile (40 001 spheres: 528 ms; this kernel 500 ms) and against k_trace_paths_l where that
+// one fits (10 001 spheres: 508 vs 473 ms), which is why the resident kernel keeps the scenes it can hold.
+// dynamic smem: 8 * RAYS * THREADS mask words + (THREADS / 32) * 2 * STREAM_CHUNK_F4 float4.
+template <int THREADS, int RAYS>
+__global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_constant__ TraceParamsL PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
-    float4* s_slab = smem4 + 8 * RAYS * THREADS / 4;
+    float4* wbuf = smem4 + 8 * RAYS * THREADS / 4 + (threadIdx.x >> 5) * (2 * STREAM_CHUNK_F4);
     const TraceConsts C = trace_consts(P);
     const unsigned lane = threadIdx.x & 31u;
     PathSlot slot[RAYS];
@@ -839,10 +901,8 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_t(const __g
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
-        const bool warp_sweeps = __any_sync(0xffffffffu, any_path);
-        // CTA-wide vote; as a barrier it also says that every warp is done with the previous trip's last tile
-        if (!__syncthreads_or(any_path ? 1 : 0)) {
-            if (__syncthreads_and((idle && exhausted) ? 1 : 0)) break;
+        if (!__any_sync(0xffffffffu, any_path)) {
+            if (__all_sync(0xffffffffu, idle && exhausted)) break;
             swept = false;
             continue;
         }
@@ -858,19 +918,8 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_t(const __g
             best_t[r] = RTB_INF;
             best_i[r] = -1;
         }
-        for (int t0 = 0; t0 < PV.n_padded; t0 += tile_spheres) {
-            const int cnt = PV.n_padded - t0 < tile_spheres ? PV.n_padded - t0 : tile_spheres;
-            if (t0 > 0) __syncthreads();                       // every warp is done with the previous tile
-            {
-                const float4* src = PV.s1 + (size_t)t0 * 3 / 4;
-                const int n4 = cnt * 3 / 4;
-                for (int i = threadIdx.x; i < n4; i += THREADS) s_slab[i] = __ldg(&src[i]);
-            }
-            __syncthreads();
-            if (warp_sweeps)                                   // a warp without a live path only keeps the barriers
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), cnt, masks, THREADS, slab,
-                                      flt, best_t, best_i, t0 / SWEEP_BLOCK);
-        }
+        sweep_two_stage_stream<RAYS>(wbuf, PV.s1, lane, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), PV.n_padded, masks, THREADS,
+                                     slab, flt, best_t, best_i);
         swept = true;
     }
     flush_counters(P, n_paths, n_segments, lane);

@@ -204,17 +204,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto k_sl = rtb::k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL>;
     constexpr int LRT = RTB_LR_THREADS;                // register-state variant of the same
     auto k_slr = rtb::k_trace_paths_l<LRT, VR>;
-    // any scene size: the same sweep over tiles of the stage-1 triples.  CTA shape (threads x CTAs per SM) from
-    // RTB200_TILED_SHAPE (tuning aid): several smaller CTAs per SM fill each other's barrier bubbles.
-    struct TiledShape { const char* name; int threads, blocks; void (*fn)(rtb::TraceParamsL, int); };
-    static const TiledShape tiled_shapes[] = {
-        {"512x1", 512, 1, rtb::k_trace_paths_t<512, 1, VR>}, {"640x1", 640, 1, rtb::k_trace_paths_t<640, 1, VR>},
-        {"256x2", 256, 2, rtb::k_trace_paths_t<256, 2, VR>}, {"320x2", 320, 2, rtb::k_trace_paths_t<320, 2, VR>},
-        {"128x4", 128, 4, rtb::k_trace_paths_t<128, 4, VR>}, {"160x4", 160, 4, rtb::k_trace_paths_t<160, 4, VR>},
-    };
-    const TiledShape* ts = &tiled_shapes[0];
-    if (const char* e = std::getenv("RTB200_TILED_SHAPE"))
-        for (const TiledShape& c : tiled_shapes) if (!std::strcmp(e, c.name)) ts = &c;
+    auto k_g = rtb::k_trace_paths_g<LRT, VR>;          // any scene size: stage-1 triples streamed per warp from global memory
     auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
     auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
     if (!ctx->attrs_set) {
@@ -224,8 +214,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         CU_TRY(cudaFuncSetAttribute(k_s2560, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_sl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_slr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        for (const TiledShape& c : tiled_shapes)
-            CU_TRY(cudaFuncSetAttribute(c.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         ctx->attrs_set = true;
@@ -245,21 +234,16 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const size_t smem_sl = (size_t)(rtb::SLOT_WORDS + CV) * VR * LT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
     const bool prefer_two = !(p->flags & RTB200_FLAG_ONE_STAGE) && ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
     const bool two_stage_smem = want != 1 && P.n_spheres > 2560 && smem_sl <= ctx->max_optin_smem && prefer_two;
-    // Tiled two-stage kernel: scenes whose stage-1 triples do not fit in shared memory at once (beyond ~10 600 spheres),
-    // whatever their layout (both filters are conservative, so it is correct for any scene; it is also the last resort
-    // of the chain below), and RTB200_FLAG_TILED.  Tile = what fits beside the stage-1 masks, in whole 32-sphere blocks;
-    // RTB200_TILE_SPHERES overrides (the parity tests run small scenes through many small tiles).
-    const size_t smem_masks_t = (size_t)8 * VR * ts->threads * sizeof(uint32_t);
-    const size_t smem_cta_t = ts->blocks == 1 ? ctx->max_optin_smem : per_sm / ts->blocks - 1024;   // 1 KB per CTA is the system's
-    int tile_spheres = (int)((smem_cta_t - smem_masks_t) / (3 * sizeof(float))) / 32 * 32;
-    if (const char* e = std::getenv("RTB200_TILE_SPHERES")) { int v = std::atoi(e) / 32 * 32; if (v >= 32 && v <= tile_spheres) tile_spheres = v; }
-    if (tile_spheres > ctx->n_padded) tile_spheres = ctx->n_padded;
-    const bool tiled = (p->flags & RTB200_FLAG_TILED) || (want != 1 && P.n_spheres > 2560 && smem_sl > ctx->max_optin_smem && prefer_two);
-    auto launch_tiled = [&]() {
+    // Streamed two-stage kernel: scenes whose stage-1 triples do not fit in shared memory at once (beyond ~10 600
+    // spheres), whatever their layout (both filters are conservative, so it is correct for any scene; it is also the
+    // last resort of the chain below), and RTB200_FLAG_STREAMED.
+    const bool streamed = (p->flags & RTB200_FLAG_STREAMED) || (want != 1 && P.n_spheres > 2560 && smem_sl > ctx->max_optin_smem && prefer_two);
+    auto launch_streamed = [&]() {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
-        ts->fn<<<sms * ts->blocks, ts->threads, smem_masks_t + (size_t)tile_spheres * 3 * sizeof(float), st>>>(pl, tile_spheres);
+        const size_t smem_g = (size_t)8 * VR * LRT * sizeof(uint32_t) + (size_t)(LRT / 32) * 2 * rtb::STREAM_CHUNK_F4 * sizeof(float4);
+        k_g<<<sms, LRT, smem_g, st>>>(pl);
     };
     auto fill_s = [&](auto* ps) {
         ps->b = P;
@@ -267,8 +251,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         ps->rp_min = ctx->slab_rp_min;
         std::memcpy(ps->s1, ctx->h_slab.data(), ctx->h_slab.size() * sizeof(float));
     };
-    if (tiled) {
-        launch_tiled();
+    if (streamed) {
+        launch_streamed();
     } else if (two_stage && P.n_spheres <= 512) {
         auto* ps = reinterpret_cast<PS512*>(ctx->h_params.data());
         fill_s(ps);
@@ -299,7 +283,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     } else if (smem_l1 <= ctx->max_optin_smem) {
         k_l1<<<sms, LARGE_THREADS, smem_l1, st>>>(P);
     } else {
-        launch_tiled();                                    // nothing else holds the scene
+        launch_streamed();                                 // nothing else holds the scene
     }
     CU_TRY(cudaGetLastError());
     ctx->launches++;

@@ -52,7 +52,7 @@ class CudaRenderer(Renderer):
         """rays_per_lane: 0 = the library's default trace kernel, 1 / 2 = force that variant (RTB200_FLAG_RAYS1/2).
         stages: 0 = the library decides, 1 / 2 = force the one- / two-stage sweep (RTB200_FLAG_ONE_STAGE / _TWO_STAGE),
         3 = two-stage with the path state in shared memory (adds RTB200_FLAG_SHARED_STATE; matters beyond 2560 spheres),
-        4 = the tiled two-stage kernel (RTB200_FLAG_TILED: what scenes beyond ~10 600 spheres get)."""
+        4 = the streamed two-stage kernel (RTB200_FLAG_STREAMED: what scenes beyond ~10 600 spheres get)."""
         self.rays_per_lane = int(rays_per_lane)
         self.stages = int(stages)
         self._ctx = C.c_void_p()

@@ -71,7 +71,7 @@ def ten_k_spheres(seed: int = 20240608) -> Scene:
 
 def forty_k_spheres(seed: int = 20240610) -> Scene:
     """Beyond the BASELINE configs: 200x200 jittered grid + ground = 40 001 spheres, the scene size at which the stage-1
-    data no longer fit in shared memory at once (three tiles of the tiled trace kernel)."""
+    data no longer fit in shared memory at once (the streamed trace kernel)."""
     return _grid_scene(100, seed, 0.80, 0.15, big=False)
 
 

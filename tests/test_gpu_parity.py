@@ -315,25 +315,24 @@ def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, st
     assert np.array_equal(img, ref_rgb)
 
 
-@pytest.mark.parametrize("tile", [32, 96, 1024, 0])
 @pytest.mark.parametrize("scene_name,W,H,spp", [("three_spheres", 96, 54, 8), ("random_spheres", 96, 54, 4), ("tube", 96, 54, 4),
-                                                ("grid28", 64, 36, 2)])
-def test_tiled_kernel_matches_oracle(rtb, renderer, oracle, monkeypatch, scene_name, W, H, spp, tile):
-    """RTB200_FLAG_TILED (stages=4): the kernel scenes beyond ~10 600 spheres get, forced onto small scenes with tiles of
-    32 / 96 / 1024 spheres (RTB200_TILE_SPHERES) so that they cross many tile boundaries — ragged last tile, a one-tile
-    scene, candidates of one ray in several tiles (the tube) — and with the library's own tile size (0)."""
+                                                ("grid28", 64, 36, 2), ("empty", 32, 18, 2), ("one_block", 64, 36, 4)])
+def test_streamed_kernel_matches_oracle(rtb, renderer, oracle, scene_name, W, H, spp):
+    """RTB200_FLAG_STREAMED (stages=4): the kernel scenes beyond ~10 600 spheres get, forced onto small scenes: fewer
+    spheres than one 256-sphere chunk, a ragged last chunk, candidates of one ray in many chunks (the tube), an odd and
+    an even number of chunks (the double buffer), no spheres at all."""
     cam = None
     if scene_name == "tube":
         scene = _tube_scene(rtb, 700)
         cam = rtb.Camera(W, H, 1.0, 40.0, (0.3, 0.2, 2.0), (0.0, 0.0, -10.0), (0.0, 1.0, 0.0), 0.0)
     elif scene_name == "grid28":
         scene = rtb.scenes._grid_scene(28, 105, 0.6, 0.25, big=False)
+    elif scene_name == "empty":
+        scene = rtb.Scene.from_list([], {})
+    elif scene_name == "one_block":
+        scene = rtb.scenes._grid_scene(2, 5, 0.5, 0.25, big=False)          # 17 spheres: half a block
     else:
         scene = getattr(rtb.scenes, scene_name)()
-    if tile:
-        monkeypatch.setenv("RTB200_TILE_SPHERES", str(tile))
-    else:
-        monkeypatch.delenv("RTB200_TILE_SPHERES", raising=False)
     renderer.stages = 4
     try:
         img, lin, stat, ref_sum, ref_rgb, ref_seg = _render_both(rtb, renderer, oracle, scene, W, H, spp, 50, camera=cam)
@@ -347,7 +346,7 @@ def test_tiled_kernel_matches_oracle(rtb, renderer, oracle, monkeypatch, scene_n
 @pytest.mark.parametrize("half,both_roots", [(55, False), (75, False), (75, True)])
 def test_render_scene_beyond_shared_memory_matches_oracle(rtb, renderer, oracle, half, both_roots):
     """Scenes whose stage-1 data no longer fit in shared memory at once (12 101 and 22 501 spheres; the reference has no
-    limit on Vec<Object>, src/ray_tracing.rs:102-104): the library's own choice must be the tiled kernel (two tiles), and
+    limit on Vec<Object>, src/ray_tracing.rs:102-104): the library's own choice is the streamed kernel, and
     the image, segment count and RGB8 output equal the oracle's."""
     scene = rtb.scenes._grid_scene(half, 300 + half, 0.6, 0.25, big=False)
     assert len(scene) == (2 * half) ** 2 + 1
