@@ -343,6 +343,19 @@ def emit(line: dict) -> None:
     out.flush()
 
 
+def _resolve_workload(name: str) -> None:
+    """G<half>: scene-size sweep workloads, registered on demand."""
+    if name in WORKLOADS:
+        return
+    if name.startswith("G") and name[1:].isdigit():
+        half = int(name[1:])
+        scenes = importlib.import_module(PKG + ".scenes")
+        setattr(scenes, "_bench_" + name, lambda: scenes._grid_scene(half, 1000 + half, 0.80, 0.15, big=False))
+        WORKLOADS[name] = ("_bench_" + name, 1920, 1080, 16, 50)
+        return
+    raise SystemExit(f"unknown workload {name}")
+
+
 def main():
     # Libraries (NCCL prints its version banner) write to file descriptor 1: keep the real stdout for the JSON line
     # and send everything else to stderr.
@@ -355,13 +368,15 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="C2", help="one of " + ", ".join(sorted(WORKLOADS)) + ", or G<half>: a (2*half)^2 + 1 sphere jittered grid "
+                    "at 1920x1080 x 16 spp (scene-size sweeps)")
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2, 3, 4], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage, 3 = two-stage with shared-memory path state, 4 = streamed two-stage (any scene size)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()
+    _resolve_workload(args.workload)
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 1)
     if args.impl == "reference":

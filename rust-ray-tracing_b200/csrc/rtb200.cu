@@ -62,7 +62,7 @@ struct rtb200_ctx {
     int up_axis = 1;                                   // the axis the slab test drops
     float slab_rp_min = 1.0f;                          // smallest floored R' of the scene (rt_filter.h make_slab_ray)
     double slab_pass = 1.0;                            // estimated fraction of pairs that pass stage 1
-    std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsS<2560>) + 64);
+    std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsV<1024>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
     float4* d_pairs = nullptr;                         // {filter, exact} interleaved per sphere (two-stage refine walk)
@@ -195,11 +195,11 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     using PV512 = rtb::TraceParamsV<512>;
     using PV1024 = rtb::TraceParamsV<1024>;
     using PS512 = rtb::TraceParamsS<512>;
-    using PS2560 = rtb::TraceParamsS<2560>;
+    using PS768 = rtb::TraceParamsS<768>;
     auto k_v512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV512>;
     auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV1024>;
     auto k_s512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS512>;
-    auto k_s2560 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS2560>;
+    auto k_s768 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS768>;
     constexpr int LT = 512;                            // shared-memory two-stage variant: one 512-thread CTA per SM
     auto k_sl = rtb::k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL>;
     constexpr int LRT = RTB_LR_THREADS;                // register-state variant of the same
@@ -211,7 +211,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         CU_TRY(cudaFuncSetAttribute(k_v512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_v1024, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_s512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_s2560, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        CU_TRY(cudaFuncSetAttribute(k_s768, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_sl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_slr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
         CU_TRY(cudaFuncSetAttribute(k_g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
@@ -228,16 +228,25 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const bool fits_v = want != 1 && (smem_v + 1024) * 4 <= per_sm;
     // two-stage (slab test first) when the scene's layout lets stage 1 reject most pairs; RTB200_FLAG_ONE_STAGE forces
     // the single-stage parameter-space kernel, RTB200_FLAG_TWO_STAGE the two-stage one.
-    const bool two_stage = fits_v && P.n_spheres <= 2560 && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
+    // Stage-1 triples go through kernel parameter space (uniform-register operands) only while they stay resident in
+    // the SM's constant cache: up to PARAM_MAX = 768 spheres (9 KB).  Measured on jittered-grid scenes (1920x1080x16 spp,
+    // parameter space vs staged in shared memory): 257 spheres 5.03 vs 4.52 ms, 485: 8.23 vs 7.47, 785: 12.2 vs 11.9,
+    // 1297: 24.3 vs 18.9, 1937: 40.4 vs 26.1, 2501: 56.8 vs 33.0 — the indexed LDCU sweep thrashes the constant cache
+    // beyond ~10 KB; C2 (486 spheres, 100 spp): 44.75 vs 46.6 ms in favour of parameter space.  RTB200_PARAM_MAX
+    // overrides (tuning aid).
+    constexpr int PARAM_MAX = 768;
+    int param_max = PARAM_MAX;
+    if (const char* e = std::getenv("RTB200_PARAM_MAX")) { int v = std::atoi(e); if (v >= 0 && v <= PARAM_MAX) param_max = v; }
+    const bool two_stage = fits_v && P.n_spheres <= param_max && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
                            ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
     const bool use_v = fits_v && !two_stage && P.n_spheres <= 1024;
     const size_t smem_sl = (size_t)(rtb::SLOT_WORDS + CV) * VR * LT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
     const bool prefer_two = !(p->flags & RTB200_FLAG_ONE_STAGE) && ((p->flags & RTB200_FLAG_TWO_STAGE) || ctx->slab_pass <= 0.12);
-    const bool two_stage_smem = want != 1 && P.n_spheres > 2560 && smem_sl <= ctx->max_optin_smem && prefer_two;
+    const bool two_stage_smem = want != 1 && P.n_spheres > param_max && smem_sl <= ctx->max_optin_smem && prefer_two;
     // Streamed two-stage kernel: scenes whose stage-1 triples do not fit in shared memory at once (beyond ~10 600
     // spheres), whatever their layout (both filters are conservative, so it is correct for any scene; it is also the
     // last resort of the chain below), and RTB200_FLAG_STREAMED.
-    const bool streamed = (p->flags & RTB200_FLAG_STREAMED) || (want != 1 && P.n_spheres > 2560 && smem_sl > ctx->max_optin_smem && prefer_two);
+    const bool streamed = (p->flags & RTB200_FLAG_STREAMED) || (want != 1 && P.n_spheres > param_max && smem_sl > ctx->max_optin_smem && prefer_two);
     auto launch_streamed = [&]() {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
@@ -258,9 +267,9 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         fill_s(ps);
         k_s512<<<sms * 4, VT, smem_v, st>>>(*ps);
     } else if (two_stage) {
-        auto* ps = reinterpret_cast<PS2560*>(ctx->h_params.data());
+        auto* ps = reinterpret_cast<PS768*>(ctx->h_params.data());
         fill_s(ps);
-        k_s2560<<<sms * 4, VT, smem_v, st>>>(*ps);
+        k_s768<<<sms * 4, VT, smem_v, st>>>(*ps);
     } else if (two_stage_smem) {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);

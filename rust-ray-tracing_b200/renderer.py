@@ -59,7 +59,7 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_create(int(device), C.byref(self._ctx)))
         self.device = int(device)
         self.seed = int(seed)
-        self._scene_id = None
+        self._scene = None        # the uploaded Scene object itself (kept alive: identity, not id(), decides re-uploads)
         self._keep = None
         self._pinned = []
 
@@ -125,7 +125,7 @@ class CudaRenderer(Renderer):
     def upload_scene(self, scene: Scene) -> None:
         sc, keep = scene.to_abi()
         _abi.check(_abi.lib.rtb200_upload_scene(self._ctx, C.byref(sc)))
-        self._scene_id = id(scene)
+        self._scene = scene
         self._keep = keep
         self.n_spheres = len(scene)
 
@@ -141,7 +141,7 @@ class CudaRenderer(Renderer):
         """Renderer::render (src/renderer.rs:38-40).  Returns (image[H,W,3] uint8, RenderStat); with want_linear=True
         returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat).  `out`: optional [H,W,3] uint8 buffer to
         receive the image (e.g. from pinned_empty) instead of a fresh array."""
-        if self._scene_id != id(scene):
+        if self._scene is not scene:
             self.upload_scene(scene)
         W, H = camera.image_width(), camera.image_height()
         if out is not None:
@@ -161,7 +161,7 @@ class CudaRenderer(Renderer):
     # ---- the sweep alone (Object::hit_packed over the scene) --------------------------------------------------
     def intersect_batch(self, scene: Scene, origins: np.ndarray, directions: np.ndarray, enabled: Optional[np.ndarray] = None):
         """Closest near-root hit per ray.  origins/directions: [n,3] float32.  Returns (index[n] int32, t[n] float32)."""
-        if self._scene_id != id(scene):
+        if self._scene is not scene:
             self.upload_scene(scene)
         o = np.ascontiguousarray(np.asarray(origins, dtype=np.float32).reshape(-1, 3).T)
         d = np.ascontiguousarray(np.asarray(directions, dtype=np.float32).reshape(-1, 3).T)

@@ -297,11 +297,13 @@ def test_candidate_list_overflow_render(rtb, renderer, oracle, n, rays, stages):
     assert np.array_equal(img, ref_rgb)
 
 
-@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 3)])
-@pytest.mark.parametrize("half", [28, 50])
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0), (2, 3), (2, 4)])
+@pytest.mark.parametrize("half", [28, 50, 54])
 def test_render_large_scene_matches_oracle(rtb, renderer, oracle, half, rays, stages):
-    """Scenes beyond the parameter-space capacity (3 137 and 10 001 spheres): the shared-memory two-stage variant with
-    the path state in registers (default) and in shared memory (stages=3), the resident one-stage variant (stages=1) and the one-ray resident variant against the oracle."""
+    """Scenes beyond the parameter-space capacity (3 137, 10 001 and 11 665 spheres — the last one past what shared memory
+    holds at once): the library's own choice (stages=0), the shared-memory two-stage variant with the path state in
+    registers (stages=2) and in shared memory (stages=3), the streamed variant (4), the resident one-stage variant
+    (stages=1) and the one-ray resident variant against the oracle."""
     scene = rtb.scenes._grid_scene(half, 77 + half, 0.6, 0.25, big=False)
     W, H, spp = 96, 54, 2
     renderer.rays_per_lane = rays
@@ -476,7 +478,7 @@ def _wild_scene(rtb, n, seed):
     return rtb.Scene.from_list(objs, mats)
 
 
-@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0), (2, 3)])
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 0), (2, 3), (2, 4)])
 @pytest.mark.parametrize("n,seed", [(300, 1), (900, 2), (3000, 3)])
 def test_render_wild_scene_matches_oracle(rtb, renderer, oracle, n, seed, rays, stages):
     scene = _wild_scene(rtb, n, seed)
