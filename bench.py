@@ -191,7 +191,11 @@ def run_ours(args):
     cam = rtb.Camera.default(W, H)
     renderer = rtb.CudaRenderer(device=local_rank, seed=1, rays_per_lane=args.rays, stages=args.stages)
     tracer = dmod.CudaTracer(renderer, scene)
-    sharded = dmod.ShardedRenderer(tracer, mode="samples", exchange=args.exchange)
+    if "x" in args.sharding:
+        gr, gs = (int(v) for v in args.sharding.split("x"))
+        sharded = dmod.ShardedRenderer(tracer, mode="grid", grid=(gr, gs), exchange=args.exchange)
+    else:
+        sharded = dmod.ShardedRenderer(tracer, mode=args.sharding, exchange=args.exchange)
     info = renderer.device_info()
 
     def barrier():
@@ -307,7 +311,7 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {gen} {W}x{H}, {spp_per_gpu} spp per GPU ({spp_total} spp total), depth {depth}",
-                       "n_spheres": n_spheres, "sharding": ("sample-range; exchange = " + {"p2p": "fused NVLink peer-memory reduce+resolve kernel (CUDA IPC), two 4-byte all-reduces as barriers",
+                       "n_spheres": n_spheres, "sharding": (("sample-range" if args.sharding == "samples" else "row-range" if args.sharding == "rows" else "grid " + args.sharding + " (row groups x sample groups)") + "; exchange = " + {"p2p": "fused NVLink peer-memory reduce+resolve kernel (CUDA IPC), two 4-byte all-reduces as barriers",
                                                                    "nccl": "NCCL reduce(sum) to rank 0 + resolve"}[sharded.exchange_in_use()])
                        if world > 1 else "single GPU",
                        "l2": "no reuse across steps: each step re-traces from the camera; inputs are KBs, the framebuffer is written once",
@@ -373,6 +377,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stages", type=int, default=0, choices=[0, 1, 2, 3, 4], help="sweep variant: 0 = library default, 1 = one-stage filter, 2 = two-stage, 3 = two-stage with shared-memory path state, 4 = streamed two-stage (any scene size)")
+    ap.add_argument("--sharding", default="samples", help="multi-GPU sharding: samples (default), rows, or RxS = R row groups x S sample groups (tile + sample)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="multi-GPU framebuffer exchange")
     ap.add_argument("--rays", type=int, default=0, choices=[0, 1, 2], help="trace kernel variant: rays per lane (0 = library default)")
     args = ap.parse_args()

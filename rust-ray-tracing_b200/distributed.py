@@ -5,7 +5,9 @@ float4 accumulation image and the partial images are summed onto rank 0 (NCCL re
 to RGB8.  Primary sharding is by SAMPLE RANGE — rank g traces samples [g*spp/G, (g+1)*spp/G) of every pixel (perfect
 balance; the Philox counter carries the global sample index, so the image does not depend on G beyond float
 summation order).  Secondary is by ROW RANGE — disjoint rows, zero elsewhere — the analogue of the reference's tile
-queue (src/renderer.rs:254-266).
+queue (src/renderer.rs:254-266).  mode="grid" combines the two (BASELINE configs[2]: "tile + sample sharded"): the ranks
+form R row groups x S sample groups, rank g = (g // S, g % S) traces its row group's rows and its sample group's samples,
+and the exchange sums the S partial images of each row group ("samples" is the grid 1 x G, "rows" is G x 1).
 
 Two exchanges are implemented (ShardedRenderer(exchange=...)):
 
@@ -143,10 +145,10 @@ class ShardedRenderer:
     Every rank calls render(); rank `dst` gets the RGB8 image, the others get None.
     """
 
-    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0, exchange: str = "auto"):
+    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0, exchange: str = "auto", grid=None):
         import torch.distributed as dist
-        if mode not in ("samples", "rows"):
-            raise ValueError("mode must be 'samples' or 'rows'")
+        if mode not in ("samples", "rows", "grid"):
+            raise ValueError("mode must be 'samples', 'rows' or 'grid'")
         if exchange not in ("auto", "p2p", "nccl"):
             raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
         self.exchange = exchange
@@ -160,11 +162,23 @@ class ShardedRenderer:
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self._accum = None
+        # R row groups x S sample groups; rank = row_group * S + sample_group
+        if mode == "samples":
+            self.grid = (1, self.world)
+        elif mode == "rows":
+            self.grid = (self.world, 1)
+        else:
+            if grid is None:
+                raise ValueError("mode='grid' needs grid=(row_groups, sample_groups)")
+            self.grid = (int(grid[0]), int(grid[1]))
+            if self.grid[0] < 1 or self.grid[1] < 1 or self.grid[0] * self.grid[1] != self.world:
+                raise ValueError(f"grid {self.grid} does not cover {self.world} ranks")
+        self.row_group, self.sample_group = divmod(self.rank, self.grid[1])
 
     def shard(self, spp_total: int, height: int):
-        if self.mode == "samples":
-            return shard_range(spp_total, self.world, self.rank), (0, height)
-        return (0, spp_total), shard_range(height, self.world, self.rank)
+        """(sample range, row range) of this rank."""
+        R, S = self.grid
+        return shard_range(spp_total, S, self.sample_group), shard_range(height, R, self.row_group)
 
     # ---- the NVLink peer-memory exchange ------------------------------------------------------------------
     def _peer_exchange(self, camera):
@@ -208,14 +222,16 @@ class ShardedRenderer:
         sample_range, row_range = self.shard(spp_total, H)
         self._trace(px.accum, max_bounces, spp_total, camera, sample_range, row_range)
         self._stream_barrier()                                   # every rank's partial image is complete
-        if self.mode == "samples":
-            # rank g reduces + resolves its contiguous slice of the pixels from ALL ranks' partial images
-            p0, p1 = shard_range(H * W, self.world, self.rank)
-            p0, p1 = (p0 + 3) // 4 * 4 if self.rank else 0, (p1 + 3) // 4 * 4 if self.rank + 1 < self.world else H * W
-            self.tracer.resolve_peers(px.peer_accum, p0, p1, spp_total, px.peer_rgb8[self.dst])
-        else:
-            # disjoint rows: every rank resolves its own rows from its own image, straight into dst's image
-            self.tracer.resolve_peers([px.accum.ptr], row_range[0] * W, row_range[1] * W, spp_total, px.peer_rgb8[self.dst])
+        # Rank (row group, sample group k) reduces + resolves the k-th slice of its row group's pixels from the partial
+        # images of the S ranks of that row group (in rank order: deterministic), straight into dst's image.  S == 1
+        # (rows): its own rows from its own image; R == 1 (samples): a slice of the whole image from every rank.
+        S = self.grid[1]
+        first, last = row_range[0] * W, row_range[1] * W
+        p0, p1 = shard_range(last - first, S, self.sample_group)
+        p0 = first + ((p0 + 3) // 4 * 4 if self.sample_group else 0)              # slices start on whole pixel quads
+        p1 = first + (p1 + 3) // 4 * 4 if self.sample_group + 1 < S else last
+        peers = [px.peer_accum[self.row_group * S + k] for k in range(S)]
+        self.tracer.resolve_peers(peers, min(p0, last), min(p1, last), spp_total, px.peer_rgb8[self.dst])
         self._stream_barrier()                                   # every slice has landed in dst's image
         if self.rank == self.dst:
             return self.tracer.torch.as_tensor(px.rgb8, device=self.tracer.device)
@@ -232,7 +248,7 @@ class ShardedRenderer:
             self._accum = self.tracer.new_accum(camera)
         accum = self._accum
         sample_range, row_range = self.shard(spp_total, H)
-        if self.mode == "rows":
+        if self.grid[0] > 1:
             accum.zero_()     # rows outside the shard must contribute zero to the sum
         self._trace(accum, max_bounces, spp_total, camera, sample_range, row_range)
         if self.world > 1:

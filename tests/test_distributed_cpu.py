@@ -40,6 +40,14 @@ class OracleTracer:
         return torch.from_numpy(v.astype(np.uint8))
 
 
+def _make_sharded(dmod, tracer, mode):
+    """mode: "samples", "rows", or "RxS" (grid of R row groups x S sample groups)."""
+    if "x" in mode:
+        r, s_ = (int(v) for v in mode.split("x"))
+        return dmod.ShardedRenderer(tracer, mode="grid", grid=(r, s_))
+    return dmod.ShardedRenderer(tracer, mode=mode)
+
+
 def _worker(rank, world, port, mode, q):
     sys.path.insert(0, ROOT)
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -52,7 +60,7 @@ def _worker(rank, world, port, mode, q):
         import oracle_lib
         scene = rtb.scenes.three_spheres()
         cam = rtb.Camera.default(W, H)
-        sr = dmod.ShardedRenderer(OracleTracer(oracle_lib, scene), mode=mode)
+        sr = _make_sharded(dmod, OracleTracer(oracle_lib, scene), mode)
         assert sr.world == world and sr.rank == rank
         img = sr.render(DEPTH, SPP, cam)
         if rank == 0:
@@ -71,12 +79,14 @@ def _free_port():
     return p
 
 
-@pytest.mark.parametrize("mode", ["samples", "rows"])
-def test_sharded_render_world2_gloo(mode, rtb, oracle):
+@pytest.mark.parametrize("mode,world", [("samples", 2), ("rows", 2), ("1x2", 2), ("2x1", 2), ("2x2", 4)])
+def test_sharded_render_gloo(mode, world, rtb, oracle):
+    """world 2: sample-range and row-range sharding and the same two written as grids; world 4: the 2 x 2 tile + sample
+    grid of BASELINE configs[2]."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, mode, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, mode, q)) for r in range(world)]
     for p in procs:
         p.start()
     got = q.get(timeout=120)
@@ -103,3 +113,21 @@ def test_shard_range_partitions_exactly(rtb):
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         dmod.shard_range(10, 2, 2)
+
+
+def test_grid_shards_cover_the_job_exactly_once(rtb):
+    """Every (row, sample) of the job belongs to exactly one rank, for every factorisation of 8 ranks."""
+    dmod = importlib.import_module("rust-ray-tracing_b200.distributed")
+
+    class Stub(dmod.ShardedRenderer):
+        def __init__(self, world, rank, grid):
+            self.world, self.rank, self.grid = world, rank, grid
+            self.row_group, self.sample_group = divmod(rank, grid[1])
+
+    Hh, spp = 37, 11
+    for R, S in [(1, 8), (2, 4), (4, 2), (8, 1)]:
+        cover = np.zeros((Hh, spp), dtype=int)
+        for rank in range(8):
+            (s0, s1), (r0, r1) = Stub(8, rank, (R, S)).shard(spp, Hh)
+            cover[r0:r1, s0:s1] += 1
+        assert np.all(cover == 1), (R, S)

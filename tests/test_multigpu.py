@@ -1,6 +1,7 @@
 """Two ranks on two GPUs (NCCL): sample-range and row-range sharding with both framebuffer exchanges — the fused NVLink
 peer-memory reduce+resolve kernel (CUDA IPC) and the NCCL reduce baseline — against the single-GPU render of the
-whole job.  Skipped on a box with fewer than two GPUs (run with `gpurun --gpus 2`)."""
+whole job; four ranks on four GPUs: the 2 x 2 tile + sample grid (BASELINE configs[2]).  Skipped on a box with fewer
+GPUs (run with `gpurun --gpus 2` / `--gpus 4`)."""
 import importlib
 import os
 import socket
@@ -15,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 W, H, SPP, DEPTH, SEED = 322, 181, 12, 50, 4      # odd sizes: pixel slices that are not multiples of 4
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, modes=(("samples", None), ("rows", None))):
     import torch
     import torch.distributed as dist
     sys.path.insert(0, ROOT)
@@ -31,15 +32,15 @@ def _worker(rank, world, port, q):
         r = rtb.CudaRenderer(device=rank, seed=SEED)
         tracer = dmod.CudaTracer(r, scene)
         out = {}
-        for mode in ("samples", "rows"):
+        for mode, grid in modes:
             for exchange in ("p2p", "nccl"):
-                sr = dmod.ShardedRenderer(tracer, mode=mode, exchange=exchange)
+                sr = dmod.ShardedRenderer(tracer, mode=mode, exchange=exchange, grid=grid)
                 a = sr.render(DEPTH, SPP, cam)
                 b = sr.render(DEPTH, SPP, cam)
                 assert sr.exchange_in_use() == exchange
                 if rank == 0:
                     assert np.array_equal(a, b)                  # deterministic
-                    out[(mode, exchange)] = a
+                    out[(mode if grid is None else "%dx%d" % grid, exchange)] = a
                 else:
                     assert a is None and b is None
                 if sr._peer is not None:
@@ -78,3 +79,30 @@ def test_two_gpu_exchanges_match_single_gpu():
         assert d.max() <= 1 and (d > 0).mean() < 1e-3
     assert np.array_equal(out[("samples", "p2p")], out[("samples", "nccl")]) or \
         np.abs(out[("samples", "p2p")].astype(int) - out[("samples", "nccl")].astype(int)).max() <= 1
+
+
+def test_four_gpu_tile_and_sample_grid_matches_single_gpu():
+    """2 row groups x 2 sample groups, 4 x 1 and 1 x 4 on four GPUs, both exchanges."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 4:
+        pytest.skip("needs four GPUs")
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    modes = (("grid", (2, 2)), ("grid", (4, 1)), ("grid", (1, 4)))
+    procs = [ctx.Process(target=_worker, args=(r, 4, port, q, modes)) for r in range(4)]
+    for p in procs:
+        p.start()
+    out, whole = q.get(timeout=600)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    for ex in ("p2p", "nccl"):
+        assert np.array_equal(out[("4x1", ex)], whole)           # disjoint rows: no summation
+        for g in ("2x2", "1x4"):                                 # partial sums added: float re-association only
+            d = np.abs(out[(g, ex)].astype(int) - whole.astype(int))
+            assert d.max() <= 1 and (d > 0).mean() < 1e-3, (g, ex)
