@@ -80,7 +80,8 @@ typedef struct rtb200_params {
     int32_t row_begin;         /* and image rows [row_begin, row_end)  (0, image_height)       */
     int32_t row_end;
     int32_t flags;             /* RTB200_FLAG_* */
-    int32_t _pad;
+    int32_t row_stride;        /* 0 or 1: every row of [row_begin, row_end); R > 1: rows row_begin, row_begin + R, ... —
+                                  interleaved scanline shards, the balanced analogue of the reference's tile queue      */
 } rtb200_params;
 
 #define RTB200_FLAG_NONE 0
@@ -208,6 +209,14 @@ int rtb200_ipc_close(rtb200_ctx* ctx, void* dev);
  * (local or a peer's).  Asynchronous on `stream`. */
 int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin,
                                 int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* stream);
+
+/* The same for a job sharded over a GRID of row groups x sample groups (tile + sample sharding): image row r was traced by
+ * row group r % row_groups (rtb200_params.row_stride = row_groups), each of whose sample_groups members holds a partial
+ * sum of that row; accum_ptrs[g * sample_groups + k] is the image of member k of row group g.  row_groups == 1 is
+ * rtb200_resolve_peers_device. */
+int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups,
+                               int32_t image_width, int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel,
+                               void* rgb8_dev, void* stream);
 
 /* Device counters of the last trace on this context (valid after the stream has been synchronised). */
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);

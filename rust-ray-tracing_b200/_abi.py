@@ -37,7 +37,7 @@ class Camera(C.Structure):
 class Params(C.Structure):
     _fields_ = [("max_bounces", C.c_int32), ("samples_per_pixel", C.c_int32), ("seed", C.c_uint64),
                 ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("flags", C.c_int32), ("_pad", C.c_int32)]
+                ("row_end", C.c_int32), ("flags", C.c_int32), ("row_stride", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -70,6 +70,7 @@ SYMBOLS = {
     "rtb200_ipc_open": (C.c_int, [_P, _P, C.POINTER(_P)]),
     "rtb200_ipc_close": (C.c_int, [_P, _P]),
     "rtb200_resolve_peers_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
+    "rtb200_resolve_grid_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtb200_launch_count": (C.c_int64, [_P]),
     "rtb200_set_hit_mode": (C.c_int32, [_P, C.c_int32]),

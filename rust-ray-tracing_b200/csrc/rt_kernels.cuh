@@ -532,7 +532,8 @@ struct TraceParams {
     int max_bounces;
     uint32_t seed_lo, seed_hi;
     int sample_begin, sample_end; // global sample indices traced by this launch
-    int row_begin, row_end;
+    int row_begin, row_end;       // image rows traced by this launch: row_begin, row_begin + row_stride, ... < row_end
+    int row_stride;               // 1 = a contiguous band; R = every R-th scanline (interleaved row shards)
     int claim_chunk;              // work items a warp takes from the queue per atomic (1..64; slot_step)
     int both_roots;               // hit mode: 0 = near root only (the reference's packed path), 1 = scalar Sphere::hit rule
     int splits_log2;              // K = 1 << splits_log2: the sample range is cut into K contiguous sub-ranges, one work item each
@@ -612,12 +613,15 @@ __device__ __forceinline__ void slot_reset(PathSlot& q) {
 struct TraceConsts {
     int W;
     uint32_t n_pix, n_items, n_samples, first_pixel, split_mask;
+    uint32_t row_skip;            // (row_stride - 1) * W: image pixels between two consecutive traced rows, 0 for a band
 };
 
 __device__ __forceinline__ TraceConsts trace_consts(const TraceParams& P) {
     TraceConsts c;
     c.W = P.cam.width;
-    c.n_pix = (uint32_t)(P.row_end - P.row_begin) * (uint32_t)c.W;
+    const int stride = P.row_stride > 1 ? P.row_stride : 1;
+    c.n_pix = (uint32_t)((P.row_end - P.row_begin + stride - 1) / stride) * (uint32_t)c.W;   // traced rows x W
+    c.row_skip = (uint32_t)(stride - 1) * (uint32_t)c.W;
     c.n_items = c.n_pix << P.splits_log2;                     // host guarantees < 2^32
     c.n_samples = (uint32_t)(P.sample_end - P.sample_begin);
     c.first_pixel = (uint32_t)P.row_begin * (uint32_t)c.W;
@@ -628,6 +632,17 @@ __device__ __forceinline__ TraceConsts trace_consts(const TraceParams& P) {
 // Sample range [begin, end) of split `split` of an item.
 __device__ __forceinline__ int split_sample(const TraceParams& P, const TraceConsts& C, uint32_t split) {
     return P.sample_begin + (int)(((unsigned long long)split * C.n_samples) >> P.splits_log2);
+}
+
+// Image pixel index (row * W + col) of the launch's local pixel `pix` (traced rows are numbered consecutively).
+__device__ __forceinline__ uint32_t image_pixel(const TraceParams& P, const TraceConsts& C, uint32_t pix) {
+    uint32_t off = 0;
+    if (C.row_skip) {                                      // interleaved rows (warp-uniform branch)
+        uint32_t lrow = P.width_magic ? __umulhi(pix, P.width_magic) : pix;   // pix / W
+        if (lrow * (uint32_t)C.W > pix) lrow--;
+        off = lrow * C.row_skip;
+    }
+    return C.first_pixel + pix + off;
 }
 
 // One loop trip of one slot, steps 1-3 (warp-collective: every lane of the warp calls it together):
@@ -658,7 +673,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
         const int s_end = split_sample(P, C, split + 1);
         if (q.s >= s_end) {
             const int n_s = s_end - split_sample(P, C, split);
-            const uint32_t out_off = (P.splits_log2 == 0) ? C.first_pixel + pix : split * C.n_pix + pix;
+            const uint32_t out_off = (P.splits_log2 == 0) ? image_pixel(P, C, pix) : split * C.n_pix + pix;
             P.out[out_off] = make_float4(q.acc.x, q.acc.y, q.acc.z, (float)n_s);
             q.item = NO_ITEM;
         }
@@ -709,7 +724,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     bool regen = false;
     uint32_t pixel_id = 0;
     if (q.item != NO_ITEM) {
-        pixel_id = C.first_pixel + (q.item >> P.splits_log2);
+        pixel_id = image_pixel(P, C, q.item >> P.splits_log2);
         regen = !q.has_path && q.s < split_sample(P, C, (q.item & C.split_mask) + 1);
     }
     if (regen || q.has_path) {
@@ -1035,7 +1050,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
     flush_counters(P, n_paths, n_segments, lane);
 }
 // ---- combine: accum[row range] = sum_k partial[k] in plane order (deterministic) -----------------------------------
-__global__ void __launch_bounds__(256) k_combine(const float4* __restrict__ partial, int splits, long long n_pix, float4* __restrict__ out) {
+// out = the image at the launch's first traced row; width / row_skip map a local pixel to its image pixel when the traced
+// rows are interleaved (row_skip = (row_stride - 1) * width, 0 for a contiguous band).
+__global__ void __launch_bounds__(256) k_combine(const float4* __restrict__ partial, int splits, long long n_pix, float4* __restrict__ out, int width,
+                                                 long long row_skip) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pix) return;
     float4 acc = partial[i];
@@ -1043,7 +1061,7 @@ __global__ void __launch_bounds__(256) k_combine(const float4* __restrict__ part
         float4 v = partial[(long long)k * n_pix + i];
         acc.x = __fadd_rn(acc.x, v.x); acc.y = __fadd_rn(acc.y, v.y); acc.z = __fadd_rn(acc.z, v.z); acc.w = __fadd_rn(acc.w, v.w);
     }
-    out[i] = acc;
+    out[row_skip ? i + (i / width) * row_skip : i] = acc;
 }
 
 // ---- K3: resolve.  4 pixels per thread: four float4 loads -> three packed u32 stores (12 bytes of RGB8). -------------
@@ -1074,11 +1092,16 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 // bytes of RGB8 (possibly into a peer's image).  All loads of a thread are issued before the first add.
 struct PeerPtrs { const float4* p[16]; };
 
-__global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ PeerPtrs peers, int n_peers, long long pixel_begin, long long pixel_end, float spp,
-                                                       uint8_t* __restrict__ rgb8) {
+__global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ PeerPtrs peers, int n_peers, int row_groups, int width, long long pixel_begin,
+                                                       long long pixel_end, float spp, uint8_t* __restrict__ rgb8) {
+    // peers.p[g * n_peers + k]: partial image of sample group k of row group g; image row r belongs to row group
+    // r % row_groups (interleaved scanlines).  row_groups == 1: every pixel sums peers.p[0 .. n_peers).
     long long p0 = pixel_begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
     if (p0 >= pixel_end) return;
     const int n = (int)((pixel_end - p0) < 4 ? (pixel_end - p0) : 4);
+    int base[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) base[k] = row_groups > 1 ? (int)(((p0 + k) / width) % row_groups) * n_peers : 0;
     float4 acc[4];
 #pragma unroll
     for (int k = 0; k < 4; k++) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1088,7 +1111,7 @@ __global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ P
         for (int gg = 0; gg < 4; gg++)
 #pragma unroll
             for (int k = 0; k < 4; k++)
-                v[gg][k] = (g + gg < n_peers && k < n) ? peers.p[g + gg][p0 + k] : make_float4(0.f, 0.f, 0.f, 0.f);
+                v[gg][k] = (g + gg < n_peers && k < n) ? peers.p[base[k] + g + gg][p0 + k] : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int gg = 0; gg < 4; gg++)
 #pragma unroll

@@ -117,6 +117,7 @@ int validate_params(const rtb200_ctx* ctx, const rtb200_camera* cam, const rtb20
     if (p->samples_per_pixel <= 0) return fail(RTB200_ERR_INVALID, "samples_per_pixel must be positive");
     if (p->sample_begin < 0 || p->sample_end < p->sample_begin) return fail(RTB200_ERR_INVALID, "bad sample range");
     if (p->row_begin < 0 || p->row_end < p->row_begin || p->row_end > cam->image_height) return fail(RTB200_ERR_INVALID, "bad row range");
+    if (p->row_stride < 0) return fail(RTB200_ERR_INVALID, "row_stride must be >= 0");
     return RTB200_OK;
 }
 
@@ -141,7 +142,8 @@ int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
 
 int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p, float4* accum, cudaStream_t st) {
     const int W = cam->image_width;
-    const long long n_pix = (long long)(p->row_end - p->row_begin) * W;
+    const int row_stride = p->row_stride > 1 ? p->row_stride : 1;
+    const long long n_pix = (long long)((p->row_end - p->row_begin + row_stride - 1) / row_stride) * W;   // traced rows x W
     CU_TRY(cudaMemsetAsync(ctx->d_counters, 0, 3 * sizeof(unsigned long long), st));
     if (n_pix == 0) return RTB200_OK;
     const int n_samples = p->sample_end - p->sample_begin;
@@ -152,7 +154,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
     P.sample_begin = p->sample_begin; P.sample_end = p->sample_end;
-    P.row_begin = p->row_begin; P.row_end = p->row_end;
+    P.row_begin = p->row_begin; P.row_end = p->row_end; P.row_stride = row_stride;
     P.both_roots = (ctx->hit_mode == RTB200_HIT_BOTH_ROOTS || (p->flags & RTB200_FLAG_BOTH_ROOTS)) ? 1 : 0;
     P.splits_log2 = choose_splits_log2(ctx, n_pix, n_samples);
     const int splits = 1 << P.splits_log2;
@@ -298,7 +300,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     ctx->launches++;
     if (splits > 1) {
         int blocks = (int)((n_pix + 255) / 256);
-        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, splits, n_pix, accum + (size_t)p->row_begin * W);
+        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, splits, n_pix, accum + (size_t)p->row_begin * W, W, (long long)(row_stride - 1) * W);
         CU_TRY(cudaGetLastError());
         ctx->launches++;
     }
@@ -606,7 +608,7 @@ int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_par
         if (rc) return rc;
     }
     cudaStream_t st = 0;
-    const bool full_rows = params->row_begin == 0 && params->row_end == camera->image_height;
+    const bool full_rows = params->row_begin == 0 && params->row_end == camera->image_height && params->row_stride <= 1;
     if (!full_rows) CU_TRY(cudaMemsetAsync(ctx->d_accum, 0, n_pix * sizeof(float4), st));
     CU_TRY(cudaEventRecord(ctx->ev[0], st));
     rc = launch_trace(ctx, camera, params, ctx->d_accum, st);
@@ -702,14 +704,17 @@ int rtb200_ipc_close(rtb200_ctx* ctx, void* dev) {
     return RTB200_OK;
 }
 
-int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin, int64_t pixel_end,
-                                int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups, int32_t image_width,
+                               int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
     if (!ctx || !accum_ptrs || !rgb8_dev) return fail(RTB200_ERR_INVALID, "null argument");
-    if (n_peers < 1 || n_peers > RTB200_MAX_PEERS) return fail(RTB200_ERR_INVALID, "n_peers must be 1.." + std::to_string(RTB200_MAX_PEERS));
+    if (row_groups < 1 || sample_groups < 1 || (int64_t)row_groups * sample_groups > RTB200_MAX_PEERS)
+        return fail(RTB200_ERR_INVALID, "row_groups x sample_groups must be 1.." + std::to_string(RTB200_MAX_PEERS));
+    if (image_width < 1) return fail(RTB200_ERR_INVALID, "image_width must be positive");
     if (pixel_begin < 0 || pixel_end < pixel_begin || samples_per_pixel <= 0) return fail(RTB200_ERR_INVALID, "bad pixel range or sample count");
+    const int n_all = row_groups * sample_groups;
     rtb::PeerPtrs pp;
     for (int k = 0; k < RTB200_MAX_PEERS; k++) pp.p[k] = nullptr;
-    for (int k = 0; k < n_peers; k++) {
+    for (int k = 0; k < n_all; k++) {
         if (!accum_ptrs[k]) return fail(RTB200_ERR_INVALID, "null peer pointer");
         pp.p[k] = static_cast<const float4*>(accum_ptrs[k]);
     }
@@ -717,11 +722,17 @@ int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, 
     CU_TRY(cudaSetDevice(ctx->device));
     const long long quads = (pixel_end - pixel_begin + 3) / 4;
     const int blocks = (int)((quads + 255) / 256);
-    rtb::k_resolve_peers<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(pp, n_peers, pixel_begin, pixel_end, (float)samples_per_pixel,
-                                                                               static_cast<uint8_t*>(rgb8_dev));
+    rtb::k_resolve_peers<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(pp, sample_groups, row_groups, image_width, pixel_begin, pixel_end,
+                                                                               (float)samples_per_pixel, static_cast<uint8_t*>(rgb8_dev));
     CU_TRY(cudaGetLastError());
     ctx->launches++;
     return RTB200_OK;
+}
+
+int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin, int64_t pixel_end,
+                                int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+    if (n_peers < 1 || n_peers > RTB200_MAX_PEERS) return fail(RTB200_ERR_INVALID, "n_peers must be 1.." + std::to_string(RTB200_MAX_PEERS));
+    return rtb200_resolve_grid_device(ctx, accum_ptrs, 1, n_peers, 1, pixel_begin, pixel_end, samples_per_pixel, rgb8_dev, stream);
 }
 
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {

@@ -4,10 +4,12 @@ The path shards naturally: paths are independent, so each rank tra
 float4 accumulation image and the partial images are summed onto rank 0 (NCCL reduce over NVLink), which resolves
 to RGB8.  Primary sharding is by SAMPLE RANGE — rank g traces samples [g*spp/G, (g+1)*spp/G) of every pixel (perfect
 balance; the Philox counter carries the global sample index, so the image does not depend on G beyond float
-summation order).  Secondary is by ROW RANGE — disjoint rows, zero elsewhere — the analogue of the reference's tile
-queue (src/renderer.rs:254-266).  mode="grid" combines the two (BASELINE configs[2]: "tile + sample sharded"): the ranks
-form R row groups x S sample groups, rank g = (g // S, g % S) traces its row group's rows and its sample group's samples,
-and the exchange sums the S partial images of each row group ("samples" is the grid 1 x G, "rows" is G x 1).
+summation order).  Secondary is by ROWS — disjoint scanlines, zero elsewhere — the analogue of the reference's tile
+queue (src/renderer.rs:254-266): row group g of R takes the INTERLEAVED scanlines g, g + R, g + 2R, ... (a static split
+that is balanced where contiguous bands are not: sky rows are cheap).  mode="grid" combines the two (BASELINE
+configs[2]: "tile + sample sharded"): the ranks form R row groups x S sample groups, rank g = (g // S, g % S) traces its
+row group's scanlines and its sample group's samples, and the exchange sums the S partial images of each row group
+("samples" is the grid 1 x G, "rows" is G x 1).
 
 Two exchanges are implemented (ShardedRenderer(exchange=...)):
 
@@ -58,6 +60,10 @@ class CudaTracer:
 
     def new_peer_exchange(self, dist, group, world, rank, height, width):
         return PeerExchange(self, dist, group, world, rank, height, width)
+
+    def resolve_grid(self, accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr):
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        self.r.resolve_grid_device(accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr, stream)
 
     def resolve_peers(self, accum_ptrs, pixel_begin, pixel_end, spp_total, rgb8_ptr):
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
@@ -176,9 +182,10 @@ class ShardedRenderer:
         self.row_group, self.sample_group = divmod(self.rank, self.grid[1])
 
     def shard(self, spp_total: int, height: int):
-        """(sample range, row range) of this rank."""
+        """(sample range, row range) of this rank; row range = (first, end, stride): row group g of R traces the
+        interleaved scanlines g, g + R, ... (rtb200_params.row_stride)."""
         R, S = self.grid
-        return shard_range(spp_total, S, self.sample_group), shard_range(height, R, self.row_group)
+        return shard_range(spp_total, S, self.sample_group), (min(self.row_group, height), height, R)
 
     # ---- the NVLink peer-memory exchange ------------------------------------------------------------------
     def _peer_exchange(self, camera):
@@ -222,16 +229,12 @@ class ShardedRenderer:
         sample_range, row_range = self.shard(spp_total, H)
         self._trace(px.accum, max_bounces, spp_total, camera, sample_range, row_range)
         self._stream_barrier()                                   # every rank's partial image is complete
-        # Rank (row group, sample group k) reduces + resolves the k-th slice of its row group's pixels from the partial
-        # images of the S ranks of that row group (in rank order: deterministic), straight into dst's image.  S == 1
-        # (rows): its own rows from its own image; R == 1 (samples): a slice of the whole image from every rank.
-        S = self.grid[1]
-        first, last = row_range[0] * W, row_range[1] * W
-        p0, p1 = shard_range(last - first, S, self.sample_group)
-        p0 = first + ((p0 + 3) // 4 * 4 if self.sample_group else 0)              # slices start on whole pixel quads
-        p1 = first + (p1 + 3) // 4 * 4 if self.sample_group + 1 < S else last
-        peers = [px.peer_accum[self.row_group * S + k] for k in range(S)]
-        self.tracer.resolve_peers(peers, min(p0, last), min(p1, last), spp_total, px.peer_rgb8[self.dst])
+        # Every rank reduces + resolves one contiguous slice of the image: a pixel of image row r sums the partial images
+        # of the S ranks of row group r % R (in rank order: deterministic), straight into dst's image.
+        R, S = self.grid
+        p0, p1 = shard_range(H * W, self.world, self.rank)
+        p0, p1 = (p0 + 3) // 4 * 4 if self.rank else 0, (p1 + 3) // 4 * 4 if self.rank + 1 < self.world else H * W
+        self.tracer.resolve_grid(px.peer_accum, R, S, W, min(p0, H * W), min(p1, H * W), spp_total, px.peer_rgb8[self.dst])
         self._stream_barrier()                                   # every slice has landed in dst's image
         if self.rank == self.dst:
             return self.tracer.torch.as_tensor(px.rgb8, device=self.tracer.device)

@@ -131,15 +131,16 @@ class CudaRenderer(Renderer):
 
     def _params(self, max_bounces, spp, camera, sample_range, row_range) -> _abi.Params:
         s0, s1 = sample_range if sample_range is not None else (0, spp)
-        r0, r1 = row_range if row_range is not None else (0, camera.image_height())
+        r0, r1, rs = (tuple(row_range) + (1,))[:3] if row_range is not None else (0, camera.image_height(), 1)
         flags = {0: 0, 1: 1, 2: 2}[self.rays_per_lane] | {0: 0, 1: 4, 2: 8, 3: 8 | 32, 4: 64}[self.stages]
-        return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), flags, 0)
+        return _abi.Params(int(max_bounces), int(spp), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), flags, int(rs))
 
     # ---- Renderer::render -------------------------------------------------------------------------------------
     def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera, *, want_linear: bool = False,
                sample_range=None, row_range=None, out: Optional[np.ndarray] = None):
         """Renderer::render (src/renderer.rs:38-40).  Returns (image[H,W,3] uint8, RenderStat); with want_linear=True
-        returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat).  `out`: optional [H,W,3] uint8 buffer to
+        returns (image, linear[H,W,4] float32 per-pixel SUM, RenderStat).  row_range: (first, end) or (first, end, stride) —
+        stride R traces every R-th scanline from `first` (interleaved row shards).  `out`: optional [H,W,3] uint8 buffer to
         receive the image (e.g. from pinned_empty) instead of a fresh array."""
         if self._scene is not scene:
             self.upload_scene(scene)
@@ -223,6 +224,16 @@ class CudaRenderer(Renderer):
         arr = (C.c_void_p * len(accum_ptrs))(*[C.c_void_p(p) for p in accum_ptrs])
         _abi.check(_abi.lib.rtb200_resolve_peers_device(self._ctx, arr, len(accum_ptrs), int(pixel_begin), int(pixel_end),
                                                         int(samples_per_pixel), C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
+
+    def resolve_grid_device(self, accum_ptrs, row_groups: int, sample_groups: int, image_width: int, pixel_begin: int, pixel_end: int,
+                            samples_per_pixel: int, rgb8_ptr: int, stream: int = 0) -> None:
+        """The same for a grid of row groups x sample groups: image row r sums the partial images
+        accum_ptrs[(r % row_groups) * sample_groups + k], k < sample_groups (rtb200_resolve_grid_device)."""
+        if len(accum_ptrs) != row_groups * sample_groups:
+            raise ValueError("accum_ptrs must hold row_groups * sample_groups pointers")
+        arr = (C.c_void_p * len(accum_ptrs))(*[C.c_void_p(p) for p in accum_ptrs])
+        _abi.check(_abi.lib.rtb200_resolve_grid_device(self._ctx, arr, int(row_groups), int(sample_groups), int(image_width), int(pixel_begin),
+                                                       int(pixel_end), int(samples_per_pixel), C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
 
     def read_counters(self) -> Tuple[int, int]:
         p, s = C.c_uint64(), C.c_uint64()

@@ -27,11 +27,11 @@ class OracleTracer:
         return torch.zeros((camera.image_height(), camera.image_width(), 4), dtype=torch.float32)
 
     def trace(self, accum, max_bounces, spp_total, camera, sample_range, row_range):
+        r0, r1, rs = (tuple(row_range) + (1,))[:3]
         s, _, _ = self.oracle.render(self.arrays, camera.image_width(), camera.image_height(), camera.vectors(), spp_total, max_bounces,
-                                     seed=SEED, sample_range=sample_range, row_range=row_range, f32=True, threads=2)
-        r0, r1 = row_range
-        accum[r0:r1, :, :3] = torch.from_numpy(s[r0:r1].astype(np.float32))
-        accum[r0:r1, :, 3] = float(sample_range[1] - sample_range[0])
+                                     seed=SEED, sample_range=sample_range, row_range=(r0, r1), f32=True, threads=2)
+        accum[r0:r1:rs, :, :3] = torch.from_numpy(s[r0:r1:rs].astype(np.float32))     # the double traces the band, keeps its scanlines
+        accum[r0:r1:rs, :, 3] = float(sample_range[1] - sample_range[0])
 
     def resolve(self, accum, spp_total):
         mean = accum[..., :3].numpy() / np.float32(spp_total)
@@ -128,6 +128,6 @@ def test_grid_shards_cover_the_job_exactly_once(rtb):
     for R, S in [(1, 8), (2, 4), (4, 2), (8, 1)]:
         cover = np.zeros((Hh, spp), dtype=int)
         for rank in range(8):
-            (s0, s1), (r0, r1) = Stub(8, rank, (R, S)).shard(spp, Hh)
-            cover[r0:r1, s0:s1] += 1
+            (s0, s1), (r0, r1, rs) = Stub(8, rank, (R, S)).shard(spp, Hh)
+            cover[r0:r1:rs, s0:s1] += 1
         assert np.all(cover == 1), (R, S)

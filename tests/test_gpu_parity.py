@@ -237,6 +237,34 @@ def test_full_size_strips_match_oracle_and_variants_agree(rtb, renderer, oracle,
         assert np.array_equal(img_v, img), (rays, stages)
 
 
+@pytest.mark.parametrize("rays,stages", VARIANTS + [(2, 4)])
+@pytest.mark.parametrize("W,H,first,stride,spp", [(96, 54, 0, 2, 4), (97, 55, 2, 3, 5), (64, 36, 5, 8, 16), (33, 7, 6, 4, 4), (1, 9, 1, 2, 3)])
+def test_interleaved_rows_match_oracle(rtb, renderer, oracle, W, H, first, stride, spp, rays, stages):
+    """rtb200_params.row_stride: every `stride`-th scanline from `first` (the interleaved row shards of the multi-GPU
+    grid).  The traced rows equal the same rows of the oracle's full frame bit for bit (the Philox counter carries the
+    image pixel index, so a pixel does not depend on which launch traces it); the other rows stay untouched (zero);
+    with and without sample splits (spp 16 on a small image splits the sample range)."""
+    scene = rtb.scenes.random_spheres()
+    cam = rtb.Camera.default(W, H)
+    renderer.seed = 11
+    renderer.rays_per_lane = rays
+    renderer.stages = stages
+    try:
+        img, lin, stat = renderer.render(50, spp, scene, cam, want_linear=True, row_range=(first, H, stride))
+    finally:
+        renderer.rays_per_lane = 0
+        renderer.stages = 0
+        renderer.seed = 1
+    ref_sum, ref_rgb, _ = oracle.render(scene.arrays(), W, H, cam.vectors(), spp, 50, seed=11, f32=True)
+    rows = np.arange(first, H, stride)
+    other = np.setdiff1d(np.arange(H), rows)
+    assert stat.paths == len(rows) * W * spp
+    assert np.abs(lin[rows][..., :3].astype(np.float64) / spp - ref_sum[rows] / spp).max() <= 1e-4
+    assert np.all(lin[rows][..., 3] == spp)
+    assert np.array_equal(img[rows], ref_rgb[rows])
+    assert np.all(lin[other] == 0) and np.all(img[other] == 0)
+
+
 def test_errors_are_reported_not_fatal(rtb, renderer):
     scene = rtb.scenes.three_spheres()
     cam = rtb.Camera.default(16, 9)

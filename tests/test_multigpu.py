@@ -72,7 +72,7 @@ def test_two_gpu_exchanges_match_single_gpu():
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    # rows: disjoint pixels, no summation -> identical; samples: two partial sums added -> float re-association only
+    # rows (interleaved scanlines): disjoint pixels, no summation -> identical; samples: two partial sums added -> float re-association only
     for ex in ("p2p", "nccl"):
         assert np.array_equal(out[("rows", ex)], whole)
         d = np.abs(out[("samples", ex)].astype(int) - whole.astype(int))
