@@ -613,15 +613,14 @@ __device__ __forceinline__ void slot_reset(PathSlot& q) {
 struct TraceConsts {
     int W;
     uint32_t n_pix, n_items, n_samples, first_pixel, split_mask;
-    uint32_t row_skip;            // (row_stride - 1) * W: image pixels between two consecutive traced rows, 0 for a band
 };
 
+template <bool STRIDED>
 __device__ __forceinline__ TraceConsts trace_consts(const TraceParams& P) {
     TraceConsts c;
     c.W = P.cam.width;
-    const int stride = P.row_stride > 1 ? P.row_stride : 1;
-    c.n_pix = (uint32_t)((P.row_end - P.row_begin + stride - 1) / stride) * (uint32_t)c.W;   // traced rows x W
-    c.row_skip = (uint32_t)(stride - 1) * (uint32_t)c.W;
+    if constexpr (STRIDED) c.n_pix = (uint32_t)((P.row_end - P.row_begin + P.row_stride - 1) / P.row_stride) * (uint32_t)c.W;   // traced rows x W
+    else c.n_pix = (uint32_t)(P.row_end - P.row_begin) * (uint32_t)c.W;
     c.n_items = c.n_pix << P.splits_log2;                     // host guarantees < 2^32
     c.n_samples = (uint32_t)(P.sample_end - P.sample_begin);
     c.first_pixel = (uint32_t)P.row_begin * (uint32_t)c.W;
@@ -635,14 +634,17 @@ __device__ __forceinline__ int split_sample(const TraceParams& P, const TraceCon
 }
 
 // Image pixel index (row * W + col) of the launch's local pixel `pix` (traced rows are numbered consecutively).
+// STRIDED is a template parameter of the trace kernels: the contiguous-band instantiations (every single-GPU render)
+// carry none of this code (as a run-time branch it cost 1.3-2 % of C2: 44.75 -> 45.3-45.7 ms).
+template <bool STRIDED>
 __device__ __forceinline__ uint32_t image_pixel(const TraceParams& P, const TraceConsts& C, uint32_t pix) {
-    uint32_t off = 0;
-    if (C.row_skip) {                                      // interleaved rows (warp-uniform branch)
+    uint32_t gp = C.first_pixel + pix;
+    if constexpr (STRIDED) {
         uint32_t lrow = P.width_magic ? __umulhi(pix, P.width_magic) : pix;   // pix / W
         if (lrow * (uint32_t)C.W > pix) lrow--;
-        off = lrow * C.row_skip;
+        gp += lrow * (uint32_t)(P.row_stride - 1) * (uint32_t)C.W;
     }
-    return C.first_pixel + pix + off;
+    return gp;
 }
 
 // One loop trip of one slot, steps 1-3 (warp-collective: every lane of the warp calls it together):
@@ -652,6 +654,7 @@ __device__ __forceinline__ uint32_t image_pixel(const TraceParams& P, const Trac
 //      (finalize + Material::get_hit_result).
 struct WarpChunk { uint32_t next = 0, end = 0; };   // the warp's private slice of the work queue (warp-uniform values)
 
+template <bool STRIDED>
 __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConsts& C, PathSlot& q, bool swept, float best_t, int best_i,
                                           bool& exhausted, WarpChunk& chunk, unsigned& n_segments, unsigned& n_paths, unsigned lane) {
     // ---- 1. terminate (src/ray_tracing.rs:353-357, :365-370) ----
@@ -673,7 +676,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
         const int s_end = split_sample(P, C, split + 1);
         if (q.s >= s_end) {
             const int n_s = s_end - split_sample(P, C, split);
-            const uint32_t out_off = (P.splits_log2 == 0) ? image_pixel(P, C, pix) : split * C.n_pix + pix;
+            const uint32_t out_off = (P.splits_log2 == 0) ? image_pixel<STRIDED>(P, C, pix) : split * C.n_pix + pix;
             P.out[out_off] = make_float4(q.acc.x, q.acc.y, q.acc.z, (float)n_s);
             q.item = NO_ITEM;
         }
@@ -724,7 +727,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     bool regen = false;
     uint32_t pixel_id = 0;
     if (q.item != NO_ITEM) {
-        pixel_id = image_pixel(P, C, q.item >> P.splits_log2);
+        pixel_id = image_pixel<STRIDED>(P, C, q.item >> P.splits_log2);
         regen = !q.has_path && q.s < split_sample(P, C, (q.item & C.split_mask) + 1);
     }
     if (regen || q.has_path) {
@@ -770,7 +773,7 @@ __device__ __forceinline__ void flush_counters(const TraceParams& P, unsigned n_
 // Persistent kernel: grid = SMs x resident CTAs.  Every loop trip runs slot_step for every slot of the lane, then makes
 // ONE closest-hit sweep for all slots of the warp.
 // dynamic smem: n_spheres float4 + RAYS * CAP * THREADS uint2.  CAP = LIST_CAP_SMALL needs n_spheres <= 32 * CAP.
-template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP>
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, bool STRIDED>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const TraceParams P) {
     extern __shared__ float4 smem4[];
     float4* s_sph = smem4;
@@ -778,7 +781,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     stage_spheres(s_sph, P.filter, 0, P.n_spheres);
     __syncthreads();
 
-    const TraceConsts C = trace_consts(P);
+    const TraceConsts C = trace_consts<STRIDED>(P);
     const unsigned lane = threadIdx.x & 31u;
     PathSlot slot[RAYS];
 #pragma unroll
@@ -796,7 +799,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -827,7 +830,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
 // only the triples and the stage-1 masks and THREADS can be larger than in the shared-state variant: more warps to hide
 // the refine walks, whose sphere records come from L2 here (the L1 is all but given to shared memory).
 // dynamic smem: 8 * RAYS * THREADS mask words + n_padded * 3 floats.
-template <int THREADS, int RAYS>
+template <int THREADS, int RAYS, bool STRIDED>
 __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_constant__ TraceParamsL PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
@@ -838,7 +841,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         for (int i = threadIdx.x; i < n4; i += THREADS) s_slab[i] = __ldg(&PV.s1[i]);
         __syncthreads();
     }
-    const TraceConsts C = trace_consts(P);
+    const TraceConsts C = trace_consts<STRIDED>(P);
     const unsigned lane = threadIdx.x & 31u;
     PathSlot slot[RAYS];
 #pragma unroll
@@ -855,7 +858,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -889,13 +892,13 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
 // CTA behind two barriers per tile (40 001 spheres: 528 ms; this kernel 500 ms) and against k_trace_paths_l where that
 // one fits (10 001 spheres: 508 vs 473 ms), which is why the resident kernel keeps the scenes it can hold.
 // dynamic smem: 8 * RAYS * THREADS mask words + (THREADS / 32) * 2 * STREAM_CHUNK_F4 float4.
-template <int THREADS, int RAYS>
+template <int THREADS, int RAYS, bool STRIDED>
 __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_constant__ TraceParamsL PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
     float4* wbuf = smem4 + 8 * RAYS * THREADS / 4 + (threadIdx.x >> 5) * (2 * STREAM_CHUNK_F4);
-    const TraceConsts C = trace_consts(P);
+    const TraceConsts C = trace_consts<STRIDED>(P);
     const unsigned lane = threadIdx.x & 31u;
     PathSlot slot[RAYS];
 #pragma unroll
@@ -912,7 +915,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -962,7 +965,7 @@ struct SmemRays {
     }
 };
 
-template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, class PV_T>
+template <int THREADS, int MIN_BLOCKS, int RAYS, int CAP, class PV_T, bool STRIDED>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __grid_constant__ PV_T PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
@@ -980,7 +983,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
         }
     }
 
-    const TraceConsts C = trace_consts(P);
+    const TraceConsts C = trace_consts<STRIDED>(P);
     const unsigned lane = threadIdx.x & 31u;
 #pragma unroll 1
     for (int r = 0; r < RAYS; r++) {
@@ -1004,7 +1007,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             q.item = W(12, r); q.s = (int)W(13, r);
             const uint32_t bw = W(14, r);
             q.bounce = (int)(bw & 0x7fffffffu); q.has_path = (bw >> 31) != 0u;
-            slot_step(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, chunk, n_segments, n_paths, lane);
             W(0, r) = __float_as_uint(q.o.x); W(1, r) = __float_as_uint(q.o.y); W(2, r) = __float_as_uint(q.o.z);
             W(3, r) = __float_as_uint(q.d.x); W(4, r) = __float_as_uint(q.d.y); W(5, r) = __float_as_uint(q.d.z);
             W(6, r) = __float_as_uint(q.thr.x); W(7, r) = __float_as_uint(q.thr.y); W(8, r) = __float_as_uint(q.thr.z);

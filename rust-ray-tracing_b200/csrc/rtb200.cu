@@ -198,29 +198,37 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     using PV1024 = rtb::TraceParamsV<1024>;
     using PS512 = rtb::TraceParamsS<512>;
     using PS768 = rtb::TraceParamsS<768>;
-    auto k_v512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV512>;
-    auto k_v1024 = rtb::k_trace_paths_v<VT, 4, VR, CV, PV1024>;
-    auto k_s512 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS512>;
-    auto k_s768 = rtb::k_trace_paths_v<VT, 4, VR, CV, PS768>;
+    // Every trace kernel exists in two instantiations: contiguous band (STRIDED = false: every single-GPU render) and
+    // interleaved scanlines (row_stride > 1).  KSEL picks by this launch's stride.
+    const bool strided = row_stride > 1;
+#define KSEL(...) (strided ? rtb::__VA_ARGS__, true> : rtb::__VA_ARGS__, false>)
+#define KBOTH(...) { CU_TRY(cudaFuncSetAttribute(rtb::__VA_ARGS__, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem)); \
+                     CU_TRY(cudaFuncSetAttribute(rtb::__VA_ARGS__, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem)); }
     constexpr int LT = 512;                            // shared-memory two-stage variant: one 512-thread CTA per SM
-    auto k_sl = rtb::k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL>;
     constexpr int LRT = RTB_LR_THREADS;                // register-state variant of the same
-    auto k_slr = rtb::k_trace_paths_l<LRT, VR>;
-    auto k_g = rtb::k_trace_paths_g<LRT, VR>;          // any scene size: stage-1 triples streamed per warp from global memory
-    auto k_m1 = rtb::k_trace_paths<SMALL_THREADS, 4, 1, CG>;
-    auto k_l1 = rtb::k_trace_paths<LARGE_THREADS, 1, 1, CG>;
+    auto k_v512 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PV512);
+    auto k_v1024 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PV1024);
+    auto k_s512 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS512);
+    auto k_s768 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS768);
+    auto k_sl = KSEL(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
+    auto k_slr = KSEL(k_trace_paths_l<LRT, VR);
+    auto k_g = KSEL(k_trace_paths_g<LRT, VR);          // any scene size: stage-1 triples streamed per warp from global memory
+    auto k_m1 = KSEL(k_trace_paths<SMALL_THREADS, 4, 1, CG);
+    auto k_l1 = KSEL(k_trace_paths<LARGE_THREADS, 1, 1, CG);
     if (!ctx->attrs_set) {
-        CU_TRY(cudaFuncSetAttribute(k_v512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_v1024, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_s512, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_s768, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_sl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_slr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_g, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_m1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        CU_TRY(cudaFuncSetAttribute(k_l1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
+        KBOTH(k_trace_paths_v<VT, 4, VR, CV, PV512);
+        KBOTH(k_trace_paths_v<VT, 4, VR, CV, PV1024);
+        KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS512);
+        KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS768);
+        KBOTH(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
+        KBOTH(k_trace_paths_l<LRT, VR);
+        KBOTH(k_trace_paths_g<LRT, VR);
+        KBOTH(k_trace_paths<SMALL_THREADS, 4, 1, CG);
+        KBOTH(k_trace_paths<LARGE_THREADS, 1, 1, CG);
         ctx->attrs_set = true;
     }
+#undef KSEL
+#undef KBOTH
     const int sms = ctx->prop.multiProcessorCount;
     const size_t per_sm = ctx->prop.sharedMemPerMultiprocessor;
     const size_t smem_v = (size_t)(rtb::SLOT_WORDS + CV) * VR * VT * sizeof(uint32_t);
