@@ -9,7 +9,9 @@
 // here (nightly Rust + portable_simd, no cargo/rustc in this image) and draws all randomness from an
 // OS-seeded thread_rng (src/ray_tracing.rs:78-79, src/geometry.rs:139-168, src/materials.rs:137).  What
 // pins this oracle is (1) hand-derived known-answer vectors for each cited routine (tests/test_oracle_kat.py,
-// SURVEY.md §8c), and (2) the Random123 known-answer vectors for Philox4x32-10.
+// SURVEY.md §8c), (2) the Random123 known-answer vectors for Philox4x32-10, and (3) the committed fixtures under
+// tests/golden/ (written from this oracle by tests/golden/make_golden.py; they freeze it against silent drift and travel to
+// the GPU box — they are NOT reference output, there is none).
 //
 // Every function cites the reference file:line it restates.  The code is templated on the scalar type:
 //   Real = double : reference-faithful arithmetic (the reference is f64 throughout, src/geometry.rs:9-13)
