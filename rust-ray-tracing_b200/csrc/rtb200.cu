@@ -14,6 +14,9 @@
 #include <thread>
 #include <vector>
 
+#ifndef RTB_LR_RAYS
+#define RTB_LR_RAYS 2       // path slots per lane of the register-state kernels (build-time tuning aid)
+#endif
 #ifndef RTB_LR_THREADS
 #define RTB_LR_THREADS 640
 #endif
@@ -193,7 +196,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     //        state in shared memory; scenes of at most N spheres (N = 512 or 1024: up to 16 KB of kernel parameters).
     //   m1 : resident kernel, 256 threads x 4 CTAs/SM, spheres staged in shared memory (up to ~2 000 spheres).
     //   l1 : resident kernel, 1024 threads x 1 CTA/SM (up to ~11 000 spheres).
-    constexpr int CG = rtb::LIST_CAP, CV = rtb::LIST_CAP_V, VT = 256, VR = 2;
+    constexpr int CG = rtb::LIST_CAP, CV = rtb::LIST_CAP_V, VT = 256, VR = 2, LR = RTB_LR_RAYS;
     using PV512 = rtb::TraceParamsV<512>;
     using PV1024 = rtb::TraceParamsV<1024>;
     using PS512 = rtb::TraceParamsS<512>;
@@ -211,8 +214,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto k_s512 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS512);
     auto k_s768 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS768);
     auto k_sl = KSEL(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
-    auto k_slr = KSEL(k_trace_paths_l<LRT, VR);
-    auto k_g = KSEL(k_trace_paths_g<LRT, VR);          // any scene size: stage-1 triples streamed per warp from global memory
+    auto k_slr = KSEL(k_trace_paths_l<LRT, LR);
+    auto k_g = KSEL(k_trace_paths_g<LRT, LR);          // any scene size: stage-1 triples streamed per warp from global memory
     auto k_m1 = KSEL(k_trace_paths<SMALL_THREADS, 4, 1, CG);
     auto k_l1 = KSEL(k_trace_paths<LARGE_THREADS, 1, 1, CG);
     if (!ctx->attrs_set) {
@@ -221,8 +224,8 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS512);
         KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS768);
         KBOTH(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
-        KBOTH(k_trace_paths_l<LRT, VR);
-        KBOTH(k_trace_paths_g<LRT, VR);
+        KBOTH(k_trace_paths_l<LRT, LR);
+        KBOTH(k_trace_paths_g<LRT, LR);
         KBOTH(k_trace_paths<SMALL_THREADS, 4, 1, CG);
         KBOTH(k_trace_paths<LARGE_THREADS, 1, 1, CG);
         ctx->attrs_set = true;
@@ -261,7 +264,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
-        const size_t smem_g = (size_t)8 * VR * LRT * sizeof(uint32_t) + (size_t)(LRT / 32) * 2 * rtb::STREAM_CHUNK_F4 * sizeof(float4);
+        const size_t smem_g = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)(LRT / 32) * 2 * rtb::STREAM_CHUNK_F4 * sizeof(float4);
         k_g<<<sms, LRT, smem_g, st>>>(pl);
     };
     auto fill_s = [&](auto* ps) {
@@ -284,7 +287,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
-        const size_t smem_slr = (size_t)8 * VR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
+        const size_t smem_slr = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
         if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) k_slr<<<sms, LRT, smem_slr, st>>>(pl);
         else k_sl<<<sms, LT, smem_sl, st>>>(pl);
     } else if (use_v && P.n_spheres <= 512) {
