@@ -84,6 +84,7 @@ struct rtb200_ctx {
     int64_t launches = 0;
     size_t max_optin_smem = 0;
     bool attrs_set = false;
+    bool intersect_attr_set = false;
     int default_rays = 0;                              // 0 = choose by scene size
 };
 
@@ -336,10 +337,9 @@ int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const fl
     int tile = padded_all < 2048 ? padded_all : 2048;    // multiple of SWEEP_BLOCK: only the last tile has a remainder
     if (tile < rtb::SWEEP_BLOCK) tile = rtb::SWEEP_BLOCK;
     size_t smem = (size_t)tile * sizeof(float4) + (size_t)rtb::LIST_CAP * threads * sizeof(uint2);
-    static bool attr = false;
-    if (!attr) {
+    if (!ctx->intersect_attr_set) {                    // function attributes are per device: one flag per context
         CU_TRY(cudaFuncSetAttribute(rtb::k_intersect_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->max_optin_smem));
-        attr = true;
+        ctx->intersect_attr_set = true;
     }
     long long blocks = (n + threads - 1) / threads;
     if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
