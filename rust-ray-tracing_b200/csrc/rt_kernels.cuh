@@ -633,6 +633,17 @@ __device__ __forceinline__ int split_sample(const TraceParams& P, const TraceCon
     return P.sample_begin + (int)(((unsigned long long)split * C.n_samples) >> P.splits_log2);
 }
 
+// Local pixel of a work item.  The queue runs through the image BOTTOM-UP (item 0 = the last pixel): the launch ends
+// when its slowest path ends (up to max_bounces loop trips after the queue ran dry), and for an upright camera the top
+// rows are sky — one-segment paths — so the expensive pixels go first and the drain is made of the cheapest work.
+#ifndef RTB_QUEUE_TOP_DOWN
+__device__ __forceinline__ uint32_t item_pixel(const TraceParams& P, const TraceConsts& C, uint32_t item) {
+    return C.n_pix - 1u - (item >> P.splits_log2);
+}
+#else
+__device__ __forceinline__ uint32_t item_pixel(const TraceParams& P, const TraceConsts&, uint32_t item) { return item >> P.splits_log2; }
+#endif
+
 // Image pixel index (row * W + col) of the launch's local pixel `pix` (traced rows are numbered consecutively).
 // STRIDED is a template parameter of the trace kernels: the contiguous-band instantiations (every single-GPU render)
 // carry none of this code (as a run-time branch it cost 1.3-2 % of C2: 44.75 -> 45.3-45.7 ms).
@@ -672,7 +683,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     }
     // ---- 2. finished items are written out; new items are claimed with one atomic per warp ----
     if (q.item != NO_ITEM && !q.has_path) {
-        const uint32_t split = q.item & C.split_mask, pix = q.item >> P.splits_log2;
+        const uint32_t split = q.item & C.split_mask, pix = item_pixel(P, C, q.item);
         const int s_end = split_sample(P, C, split + 1);
         if (q.s >= s_end) {
             const int n_s = s_end - split_sample(P, C, split);
@@ -727,7 +738,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     bool regen = false;
     uint32_t pixel_id = 0;
     if (q.item != NO_ITEM) {
-        pixel_id = image_pixel<STRIDED>(P, C, q.item >> P.splits_log2);
+        pixel_id = image_pixel<STRIDED>(P, C, item_pixel(P, C, q.item));
         regen = !q.has_path && q.s < split_sample(P, C, (q.item & C.split_mask) + 1);
     }
     if (regen || q.has_path) {
