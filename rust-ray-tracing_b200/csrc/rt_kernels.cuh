@@ -663,6 +663,29 @@ __device__ __forceinline__ uint32_t image_pixel(const TraceParams& P, const Trac
 //   2. write a finished item out and claim a new one (one atomic per warp);
 //   3. ONE Philox block: the next camera sample (Camera::get_ray) or this bounce's scatter
 //      (finalize + Material::get_hit_result).
+#ifdef RTB_TIMELINE
+// Debug builds only (tools/gpu_timeline.sh): when did the warps of a launch start, see the queue run dry, and exit?
+// g_timeline: [0] min start, [1] max start, [2] min dry, [3] max dry, [4] min exit, [5] max exit (globaltimer ns),
+// [8 + b]: warps whose exit falls into the b-th 50 us bin BEFORE the last exit is not known on the device, so the bins
+// count exits by absolute time >> 16 (65.5 us) modulo 1024 from the launch's min start (host subtracts).
+__device__ unsigned long long g_timeline[8 + 4096];
+__device__ __forceinline__ unsigned long long tl_now() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+__device__ __forceinline__ void tl_mark(int slot, unsigned lane) {
+    if (lane == 0) { const unsigned long long t = tl_now(); atomicMin(&g_timeline[slot], t); atomicMax(&g_timeline[slot + 1], t); }
+}
+__device__ __forceinline__ void tl_exit(unsigned lane) {
+    if (lane == 0) { const unsigned long long t = tl_now(); atomicMin(&g_timeline[4], t); atomicMax(&g_timeline[5], t);
+                     atomicAdd(&g_timeline[8 + ((t >> 15) & 4095)], 1ull); }
+}
+#define RTB_TL_START(lane) tl_mark(0, lane)
+#define RTB_TL_DRY(lane) tl_mark(2, lane)
+#define RTB_TL_EXIT(lane) tl_exit(lane)
+#else
+#define RTB_TL_START(lane)
+#define RTB_TL_DRY(lane)
+#define RTB_TL_EXIT(lane)
+#endif
+
 struct WarpChunk { uint32_t next = 0, end = 0; };   // the warp's private slice of the work queue (warp-uniform values)
 
 template <bool STRIDED>
@@ -714,6 +737,7 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
                 chunk.end = C.n_items - base < (uint32_t)P.claim_chunk ? C.n_items : base + (uint32_t)P.claim_chunk;
             } else {
                 exhausted = true;                      // the queue is empty: warp-uniform
+                RTB_TL_DRY(lane);
             }
             avail = chunk.end - chunk.next;
         }
@@ -1005,6 +1029,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
     }
     bool exhausted = false;
     WarpChunk chunk;
+    RTB_TL_START(lane);
     unsigned n_segments = 0, n_paths = 0;
     bool swept = false;
 
@@ -1061,6 +1086,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
         for (int r = 0; r < RAYS; r++) { W(15, r) = __float_as_uint(best_t[r]); W(16, r) = (uint32_t)best_i[r]; }
         swept = true;
     }
+    RTB_TL_EXIT(lane);
     flush_counters(P, n_paths, n_segments, lane);
 }
 // ---- combine: accum[row range] = sum_k partial[k] in plane order (deterministic) -----------------------------------

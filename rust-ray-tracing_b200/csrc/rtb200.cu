@@ -807,3 +807,16 @@ int rtb200_fp32_peak(rtb200_ctx* ctx, int32_t iters, double* tflops, double* ms_
 }
 
 }  // extern "C"
+
+#ifdef RTB_TIMELINE
+// Debug builds only: reset / read the trace kernels' timeline (rt_kernels.cuh, g_timeline).
+extern "C" int rtb200_debug_timeline(int reset, unsigned long long* out /* 8 + 4096 */) {
+    static unsigned long long init[8 + 4096];
+    if (reset) {
+        for (int i = 0; i < 8 + 4096; i++) init[i] = 0;
+        init[0] = init[2] = init[4] = ~0ull;
+        return (int)cudaMemcpyToSymbol(rtb::g_timeline, init, sizeof init);
+    }
+    return (int)cudaMemcpyFromSymbol(out, rtb::g_timeline, sizeof init);
+}
+#endif
