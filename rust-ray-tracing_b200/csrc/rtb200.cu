@@ -135,11 +135,13 @@ int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
     int lg = 0;
     // (a) fill the machine: at least two items per path slot, down to 4 samples per item (small images: C1)
     while (lg < 6 && (n_pix << lg) < 2 * slots && (n_samples >> (lg + 1)) >= 4) lg++;
-    // (b) tail balance: ~64 items per slot while an item keeps at least 6 samples on a ~500-sphere scene, fewer where
-    //     the sweeps are longer
+    // (b) tail balance: ~64 items per slot.  What matters is the NUMBER of items, not their length: on C2's geometry
+    //     (bottom-up queue, profiles/r1_splits_sweep.txt) 8 spp K = 1/2/4/8 take 5.96/4.96/4.45/4.25 ms, 16 spp K = 2/4/8/16
+    //     9.75/8.92/7.71/7.77, 25 spp K = 4/8/16 12.84/12.34/11.97, 50 spp K = 8/16/32 23.19/23.39/23.47 — so an item may
+    //     shrink to a single sample.  Longer sweeps (>= 1000 spheres) keep two samples per item: 1 297 spheres at 16 spp
+    //     K = 4/8/16 18.50/18.20/18.55 ms, 10 001 spheres 118.6/118.5/121.1.
     const int n_sph = ctx->n_spheres > 0 ? ctx->n_spheres : 1;
-    int min_samples = (2916 + n_sph - 1) / n_sph;
-    min_samples = min_samples < 2 ? 2 : (min_samples > 6 ? 6 : min_samples);
+    const int min_samples = n_sph >= 1000 ? 2 : 1;
     while (lg < 6 && (n_pix << lg) < 64 * slots && (n_samples >> (lg + 1)) >= min_samples) lg++;
     return lg;
 }
