@@ -44,3 +44,24 @@ def test_gpu_arm_refuses_to_run_without_a_device():
         pytest.skip("a GPU is present")
     r = _run(["--steps", "1", "--warmup", "1"])
     assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+
+
+@pytest.mark.gpu
+def test_gpu_arm_line_carries_the_contract_keys():
+    """The product arm on the smallest workload (C1 in full): one JSON line with roofline, e2e, clocks, gpu_launches."""
+    r = _run(["--workload", "C1", "--steps", "2", "--warmup", "3", "--no-cpu-baseline"])
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1, r.stdout
+    d = json.loads(lines[0])
+    assert "impl" not in d and d["metric"] == "Mpaths/s" and d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3
+    assert d["value"] > 0 and d["dtype"] == "f32" and d["scaling"] == "weak" and d["vs_baseline"] is None
+    assert d["config"]["workload"].startswith("C1:") and d["config"]["n_spheres"] == 4
+    rf = d["roofline"]
+    assert rf["bound"] == "fp32" and rf["unit"] == "TFLOP/s" and rf["peak"] > 20 and rf["achieved"] > 0
+    assert abs(rf["frac"] - rf["achieved"] / rf["peak"]) < 1e-9 and rf["flop_per_test"] == 17.0
+    e = d["e2e"]
+    assert e["value"] > 0 and e["value"] <= d["value"] * 1.05 and e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] == 400 * 225 * 3
+    assert d["gpu_launches"] >= 2 * 2                      # at least trace + resolve per step
+    assert d["clocks"]["sm_max_mhz"] is None or d["clocks"]["sm_max_mhz"] > 0
+    assert d["cpu_baseline"] is None                       # --no-cpu-baseline
