@@ -167,6 +167,15 @@ int rtb200_intersect_batch(rtb200_ctx* ctx, const float* ox, const float* oy, co
                            const float* dy, const float* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index,
                            float* hit_t);
 
+/* The same routine at the reference's own precision: f64 rays against the f64 spheres of the uploaded scene, every
+ * (ray, sphere) pair in list order, in the reference's operation order with its mul_add sites (src/geometry.rs:435,467;
+ * src/objects.rs:252-257) — the result equals Sphere::hit_packed + PackedHitRecords::update in f64 bit for bit.  This is
+ * the probe that measures how far the FP32 production sweep (rtb200_intersect_batch, the render kernels) is from the
+ * reference on given rays, and the call for a caller that needs f64 hit distances; rendering stays FP32. */
+int rtb200_intersect_batch_f64(rtb200_ctx* ctx, const double* ox, const double* oy, const double* oz, const double* dx,
+                               const double* dy, const double* dz, const uint8_t* enabled, int64_t n,
+                               int32_t* hit_index, double* hit_t);
+
 /* ---- the same kernels on device-resident buffers (for callers that own device memory and streams) -------- */
 
 /* Trace kernel only: accumulates the per-pixel linear SUM of the shard named by `params` into accum_dev

@@ -61,6 +61,7 @@ SYMBOLS = {
     "rtb200_upload_scene": (C.c_int, [_P, C.POINTER(Scene)]),
     "rtb200_render": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P, C.POINTER(Stats)]),
     "rtb200_intersect_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P]),
+    "rtb200_intersect_batch_f64": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P]),
     "rtb200_trace_device": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P]),
     "rtb200_resolve_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_intersect_batch_device": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),

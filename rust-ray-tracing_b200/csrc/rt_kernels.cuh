@@ -10,6 +10,7 @@
 //                     + sky + per-pixel accumulation (src/renderer.rs:141-176, src/ray_tracing.rs:77-89, :312-628,
 //                     src/materials.rs:53-147).  A lane slot = one pixel's sample stream; path regeneration replaces
 //                     the reference's lane compaction (src/ray_tracing.rs:429-483, :561-607).
+//   k_intersect_batch_f64  K1d: the same routine in f64 over f64 spheres, every pair (the reference-precision probe).
 //   k_combine         sums the K sample-split partial planes in plane order.
 //   k_resolve         K3: sum/spp + Color::to_u8_array + image assembly (src/renderer.rs:161-163, :376-384;
 //                     src/color.rs:54-64).
@@ -517,6 +518,59 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
         hit_index[i] = en ? best_i[0] : -1;
         hit_t[i] = (en && best_i[0] >= 0) ? best_t[0] : RTB_INF;
+    }
+}
+
+// ---- K1d: the reference's routine at the reference's precision ---------------------------------------------------------
+// Sphere::hit_packed + PackedHitRecords::update (src/objects.rs:249-290, :140-155) for one ray per thread in f64 — the
+// reference's own scalar type (src/geometry.rs:9-13) — over f64 spheres {cx, cy, cz, r} in list order, every pair, no
+// filter.  Same operation order and FMA sites as the reference (mul_add at src/geometry.rs:435,467 and src/objects.rs:257),
+// IEEE sqrt and division: the result equals the f64 routine bit for bit.  It is the PROBE that says how far the FP32
+// production sweep is from the reference on given rays (index equal; t to ~1e-6 median, 6e-4 worst on the ground
+// sphere), and the way to get f64 hit distances where a caller needs them; the render path stays FP32 (north_star).
+// Spheres go through shared memory in tiles of 256 (8 KB).
+__global__ void __launch_bounds__(256) k_intersect_batch_f64(const double4* __restrict__ g_sph, int n_spheres, const double* __restrict__ ox,
+                                                             const double* __restrict__ oy, const double* __restrict__ oz,
+                                                             const double* __restrict__ dx, const double* __restrict__ dy,
+                                                             const double* __restrict__ dz, const uint8_t* __restrict__ enabled, long long n_rays,
+                                                             int* __restrict__ hit_index, double* __restrict__ hit_t, int both_roots) {
+    __shared__ double4 s_sph[256];
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < n_rays;
+    double rox = 0.0, roy = 0.0, roz = 0.0, rdx = 0.0, rdy = 0.0, rdz = 1.0;
+    if (live) { rox = ox[i]; roy = oy[i]; roz = oz[i]; rdx = dx[i]; rdy = dy[i]; rdz = dz[i]; }
+    const double T_MIN_D = 0.001, INF_D = __longlong_as_double(0x7ff0000000000000LL);
+    const double a = __fma_rn(rdz, rdz, __fma_rn(rdy, rdy, __dmul_rn(rdx, rdx)));                   // src/objects.rs:253
+    const double inv_a = __ddiv_rn(1.0, a);                                                         // :254
+    double best_t = INF_D;                                                                          // PackedHitRecords::default, :121-134
+    int best_i = -1;
+    for (int begin = 0; begin < n_spheres; begin += 256) {
+        const int count = min(256, n_spheres - begin);
+        __syncthreads();
+        if ((int)threadIdx.x < count) s_sph[threadIdx.x] = g_sph[begin + threadIdx.x];
+        __syncthreads();
+        for (int j = 0; j < count; j++) {
+            const double4 sp = s_sph[j];
+            const double ocx = __dsub_rn(rox, sp.x), ocy = __dsub_rn(roy, sp.y), ocz = __dsub_rn(roz, sp.z);          // :252
+            const double hb = __fma_rn(ocz, rdz, __fma_rn(ocy, rdy, __dmul_rn(ocx, rdx)));                            // :255
+            const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), __dmul_rn(sp.w, sp.w));   // :256
+            const double disc = __fma_rn(hb, hb, -__dmul_rn(a, cc));                                                  // :257
+            if (disc >= 0.0) {                                                                                        // :259
+                const double sq = __dsqrt_rn(disc);                                                                   // :263
+                double root1 = __dmul_rn(__dsub_rn(-hb, sq), inv_a);                                                  // :270
+                bool valid = (root1 >= T_MIN_D) && (root1 < INF_D);                                                   // :272-277
+                if (!valid && both_roots) {                                                                           // scalar rule, :230-234
+                    root1 = __dmul_rn(__dadd_rn(-hb, sq), inv_a);                                                     // :271
+                    valid = (root1 >= T_MIN_D) && (root1 < INF_D);
+                }
+                if (valid && root1 <= best_t) { best_t = root1; best_i = begin + j; }                                 // :141
+            }
+        }
+    }
+    if (live) {
+        const bool en = enabled ? enabled[i] != 0 : true;                                           // rays.enabled(), :259,277
+        hit_index[i] = en ? best_i : -1;
+        hit_t[i] = (en && best_i >= 0) ? best_t : INF_D;
     }
 }
 

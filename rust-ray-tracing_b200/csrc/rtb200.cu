@@ -68,6 +68,7 @@ struct rtb200_ctx {
     std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsV<1024>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
+    double4* d_spheres64 = nullptr; size_t spheres64_count = 0;   // {cx, cy, cz, r} in f64, list order (rtb200_intersect_batch_f64)
     float4* d_pairs = nullptr;                         // {filter, exact} interleaved per sphere (two-stage refine walk)
     float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
     int n_padded = 32;
@@ -389,7 +390,7 @@ int rtb200_create(int32_t device, rtb200_ctx** out) {
 void rtb200_destroy(rtb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_scene); cudaFree(c->d_counters);
+    cudaFree(c->d_scene); cudaFree(c->d_spheres64); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->h_progress) cudaFreeHost(c->h_progress);
@@ -541,6 +542,17 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
     ctx->d_slab = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int)));   // cnt % 32 == 0: 16-byte aligned
     ctx->d_pairs = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float)));
+    {   // the scene at the reference's precision, for the f64 probe
+        if (ctx->spheres64_count < (size_t)std::max(n, 1)) {
+            cudaFree(ctx->d_spheres64);
+            ctx->d_spheres64 = nullptr; ctx->spheres64_count = 0;
+            CU_TRY(cudaMalloc(&ctx->d_spheres64, (size_t)std::max(n, 1) * sizeof(double4)));
+            ctx->spheres64_count = (size_t)std::max(n, 1);
+        }
+        std::vector<double4> s64((size_t)n);
+        for (int i = 0; i < n; i++) s64[i] = make_double4(scene->spheres[i].center[0], scene->spheres[i].center[1], scene->spheres[i].center[2], scene->spheres[i].radius);
+        if (n > 0) CU_TRY(cudaMemcpy(ctx->d_spheres64, s64.data(), (size_t)n * sizeof(double4), cudaMemcpyHostToDevice));
+    }
     ctx->n_padded = (int)cnt;
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);
@@ -599,6 +611,41 @@ int rtb200_intersect_batch(rtb200_ctx* ctx, const float* ox, const float* oy, co
     if (rc) return rc;
     CU_TRY(cudaMemcpyAsync(hit_index, d_idx, nn * sizeof(int), cudaMemcpyDeviceToHost, 0));
     CU_TRY(cudaMemcpyAsync(hit_t, d_t, nn * sizeof(float), cudaMemcpyDeviceToHost, 0));
+    CU_TRY(cudaStreamSynchronize(0));
+    return RTB200_OK;
+}
+
+int rtb200_intersect_batch_f64(rtb200_ctx* ctx, const double* ox, const double* oy, const double* oz, const double* dx, const double* dy,
+                               const double* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index, double* hit_t) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (!ctx->d_spheres) return fail(RTB200_ERR_STATE, "no scene uploaded (call rtb200_upload_scene first)");
+    if (n < 0) return fail(RTB200_ERR_INVALID, "negative ray count");
+    if (n == 0) return RTB200_OK;
+    if (!ox || !oy || !oz || !dx || !dy || !dz || !hit_index || !hit_t) return fail(RTB200_ERR_INVALID, "null ray buffer");
+    CU_TRY(cudaSetDevice(ctx->device));
+    // device scratch: 6 double planes, t plane (double), idx plane, enabled bytes
+    const size_t nn = (size_t)n;
+    int rc = ensure(&ctx->d_rays, &ctx->rays_bytes, nn * (7 * sizeof(double) + sizeof(int) + 1));
+    if (rc) return rc;
+    double* base = static_cast<double*>(ctx->d_rays);
+    const double* src[6] = {ox, oy, oz, dx, dy, dz};
+    for (int k = 0; k < 6; k++) CU_TRY(cudaMemcpyAsync(base + k * nn, src[k], nn * sizeof(double), cudaMemcpyHostToDevice, 0));
+    double* d_t = base + 6 * nn;
+    int* d_idx = reinterpret_cast<int*>(base + 7 * nn);
+    uint8_t* d_en = nullptr;
+    if (enabled) {
+        d_en = reinterpret_cast<uint8_t*>(d_idx + nn);
+        CU_TRY(cudaMemcpyAsync(d_en, enabled, nn, cudaMemcpyHostToDevice, 0));
+    }
+    const long long blocks = ((long long)n + 255) / 256;
+    if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
+    rtb::k_intersect_batch_f64<<<(unsigned)blocks, 256, 0, 0>>>(ctx->d_spheres64, ctx->n_spheres, base, base + nn, base + 2 * nn, base + 3 * nn,
+                                                               base + 4 * nn, base + 5 * nn, d_en, n, d_idx, d_t,
+                                                               ctx->hit_mode == RTB200_HIT_BOTH_ROOTS ? 1 : 0);
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    CU_TRY(cudaMemcpyAsync(hit_index, d_idx, nn * sizeof(int), cudaMemcpyDeviceToHost, 0));
+    CU_TRY(cudaMemcpyAsync(hit_t, d_t, nn * sizeof(double), cudaMemcpyDeviceToHost, 0));
     CU_TRY(cudaStreamSynchronize(0));
     return RTB200_OK;
 }

@@ -180,6 +180,27 @@ class CudaRenderer(Renderer):
                                                    _ptr(en), n, _ptr(idx), _ptr(t)))
         return idx, t
 
+    def intersect_batch_f64(self, scene: Scene, origins: np.ndarray, directions: np.ndarray, enabled: Optional[np.ndarray] = None):
+        """The same routine at the reference's precision (rtb200_intersect_batch_f64): f64 rays against the scene's f64
+        spheres, every pair.  origins/directions: [n,3] float64.  Returns (index[n] int32, t[n] float64)."""
+        if self._scene is not scene:
+            self.upload_scene(scene)
+        o = np.ascontiguousarray(np.asarray(origins, dtype=np.float64).reshape(-1, 3).T)
+        d = np.ascontiguousarray(np.asarray(directions, dtype=np.float64).reshape(-1, 3).T)
+        n = o.shape[1]
+        if d.shape[1] != n:
+            raise ValueError("origins and directions differ in length")
+        en = None
+        if enabled is not None:
+            en = np.ascontiguousarray(np.asarray(enabled).astype(np.uint8))
+            if en.shape != (n,):
+                raise ValueError("enabled mask has the wrong length")
+        idx = np.empty(n, dtype=np.int32)
+        t = np.empty(n, dtype=np.float64)
+        _abi.check(_abi.lib.rtb200_intersect_batch_f64(self._ctx, _ptr(o[0]), _ptr(o[1]), _ptr(o[2]), _ptr(d[0]), _ptr(d[1]), _ptr(d[2]),
+                                                       _ptr(en), n, _ptr(idx), _ptr(t)))
+        return idx, t
+
     # ---- device-resident entry points (torch owns the memory and the stream) ----------------------------------
     def trace_device(self, max_bounces: int, samples_per_pixel: int, camera: Camera, accum_ptr: int, stream: int = 0,
                      sample_range=None, row_range=None) -> None:

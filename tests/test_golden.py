@@ -125,3 +125,23 @@ def test_cuda_renders_the_toml_fixture(rtb, renderer):
     renderer.seed = seed
     img, stat = renderer.render(depth, spp, scene, rtb.Camera.default(W, H))
     assert np.array_equal(img, g["rgb8_f32"]) and stat.segments == int(g["segments_f32"])
+
+
+@pytest.mark.gpu
+def test_cuda_f64_probe_equals_the_f64_golden_bit_for_bit(rtb, renderer):
+    """rtb200_intersect_batch_f64: the reference's routine at the reference's precision on the device.  On the stored
+    batch it returns oracle<double>'s index and t exactly (same operation order, mul_add sites, IEEE sqrt/div) — the
+    north_star's intersection bar (index exact, t within 1e-5) with nothing to spare — and it is the yardstick for the
+    FP32 production sweep on the same rays."""
+    g = _load("intersect_random_spheres.npz")
+    scene = rtb.scenes.random_spheres()
+    rays = g["rays"]
+    idx, t = renderer.intersect_batch_f64(scene, rays[:, :3], rays[:, 3:], enabled=g["enabled"].astype(np.uint8))
+    assert np.array_equal(idx, g["idx_f64"])
+    hit = idx >= 0
+    assert np.array_equal(t[hit], g["t_f64"][hit]) and np.all(np.isinf(t[~hit]))
+    idx32, t32 = renderer.intersect_batch(scene, rays[:, :3].astype(np.float32), rays[:, 3:].astype(np.float32),
+                                          enabled=g["enabled"].astype(np.uint8))
+    assert np.array_equal(idx32, idx)                                     # the FP32 sweep against the device's own f64 probe
+    rel = np.abs(t32[hit].astype(np.float64) - t[hit]) / np.abs(t[hit])
+    assert np.median(rel) < 2e-6 and (rel <= 1e-5).mean() > 0.75 and rel.max() < 1e-3

@@ -394,6 +394,41 @@ def test_render_scene_beyond_shared_memory_matches_oracle(rtb, renderer, oracle,
     assert np.array_equal(img, ref_rgb)
 
 
+@pytest.mark.parametrize("both_roots", [False, True])
+@pytest.mark.parametrize("scene_name,m", [("three_spheres", 5000), ("dielectric_heavy", 5000), ("ten_k_spheres", 2000), ("wild", 3000), ("empty", 100)])
+def test_f64_probe_matches_the_f64_oracle(rtb, renderer, oracle, scene_name, m, both_roots):
+    """rtb200_intersect_batch_f64 against oracle<double> (the reference-faithful instantiation): index and t bit-equal on
+    f64 rays that are NOT f32-representable — camera-like, from inside the scene, non-unit, some disabled — for scenes
+    that span one to forty sphere tiles, and under the both-roots option."""
+    if scene_name == "wild":
+        scene = _wild_scene(rtb, 900, 2)
+    elif scene_name == "empty":
+        scene = rtb.Scene.from_list([], {})
+    else:
+        scene = getattr(rtb.scenes, scene_name)()
+    rng = np.random.default_rng(m + 7 * int(both_roots))
+    o = np.concatenate([np.tile([13.0, 2.0, 3.0], (m // 2, 1)) + rng.normal(0, 1e-3, (m // 2, 3)),
+                        np.stack([rng.uniform(-11, 11, m - m // 2), rng.uniform(0.05, 1.5, m - m // 2), rng.uniform(-11, 11, m - m // 2)], axis=1)])
+    d = np.concatenate([np.stack([rng.uniform(-11, 11, m // 2), rng.uniform(0, 1, m // 2), rng.uniform(-11, 11, m // 2)], axis=1) - o[: m // 2],
+                        rng.normal(size=(m - m // 2, 3)) * rng.uniform(0.1, 4.0, (m - m // 2, 1))])
+    en = (rng.random(m) > 0.05).astype(np.uint8)
+    renderer.set_hit_mode(both_roots)
+    oracle.set_both_roots(both_roots)
+    try:
+        idx, t = renderer.intersect_batch_f64(scene, o, d, enabled=en)
+        spheres = np.asarray(scene.arrays()[0], dtype=np.float64).reshape(-1, 4)
+        ridx, rt = oracle.intersect(spheres, np.concatenate([o, d], axis=1), enabled=en.astype(np.int32), f32=False)
+    finally:
+        renderer.set_hit_mode(False)
+        oracle.set_both_roots(False)
+    assert np.array_equal(idx, ridx)
+    hit = idx >= 0
+    assert np.array_equal(t[hit], rt[hit])
+    assert np.all(idx[en == 0] == -1)
+    if scene_name != "empty":
+        assert hit.mean() > 0.2
+
+
 def test_both_roots_intersect(rtb, renderer, oracle):
     """RTB200_HIT_BOTH_ROOTS (scalar Sphere::hit rule) on the GPU against the oracle with the same option."""
     S, M = rtb.Sphere, rtb.Material
