@@ -146,8 +146,8 @@ int rtb200_camera_init(rtb200_camera* out, int32_t image_width, int32_t image_he
                        double view_angle_deg, const double center[3], const double look_at[3], const double up[3],
                        double defocus_angle_deg);
 
-/* Scene::from_list (src/ray_tracing.rs:222-224): flattens the scene to the device layout
- * (float4 {cx,cy,cz,r*r} per sphere + per-sphere material records) and uploads it. */
+/* Scene::from_list (src/ray_tracing.rs:222-224): flattens the scene to the device layout (per sphere: f64 {cx,cy,cz,r*r}
+ * for the exact hit test, FP32 filter records for the all-pairs passes of the sweep, a material record) and uploads it. */
 int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene);
 
 /* ---- the render path, host buffers (the reference-facing call) ------------------------------------------- */
@@ -162,16 +162,20 @@ int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_par
 /* Scene sweep = Object::hit_packed over all objects + PackedHitRecords::update
  * (src/ray_tracing.rs:397-403, src/objects.rs:249-290, :140-155) for a batch of rays, host buffers.
  * rays: SoA float arrays of length n.  enabled: PackedRays::enabled lane mask (src/ray.rs:41), may be null (= all).
- * hit_index[i] = object index of the closest near-root hit or -1; hit_t[i] = its t, +inf on a miss. */
+ * hit_index[i] = object index of the closest near-root hit or -1; hit_t[i] = its t, +inf on a miss.
+ * Precision: the rays are FP32 (the path state of the render kernels); the hit test itself runs at the reference's
+ * precision — f64 discriminant, root and closest-hit comparison on the f64 spheres of the scene description, in the
+ * reference's operation order — so hit_index equals the f64 routine's for these rays and hit_t is its root rounded once
+ * to FP32 (relative error <= 6e-8; BASELINE.json asks for 1e-5). */
 int rtb200_intersect_batch(rtb200_ctx* ctx, const float* ox, const float* oy, const float* oz, const float* dx,
                            const float* dy, const float* dz, const uint8_t* enabled, int64_t n, int32_t* hit_index,
                            float* hit_t);
 
-/* The same routine at the reference's own precision: f64 rays against the f64 spheres of the uploaded scene, every
- * (ray, sphere) pair in list order, in the reference's operation order with its mul_add sites (src/geometry.rs:435,467;
- * src/objects.rs:252-257) — the result equals Sphere::hit_packed + PackedHitRecords::update in f64 bit for bit.  This is
- * the probe that measures how far the FP32 production sweep (rtb200_intersect_batch, the render kernels) is from the
- * reference on given rays, and the call for a caller that needs f64 hit distances; rendering stays FP32. */
+/* The same routine for f64 rays, with NO filter: f64 rays against the f64 spheres of the uploaded scene, every (ray, sphere)
+ * pair in list order, in the reference's operation order with its mul_add sites (src/geometry.rs:435,467;
+ * src/objects.rs:252-257) — the result equals Sphere::hit_packed + PackedHitRecords::update in f64 bit for bit.  The
+ * production sweep (rtb200_intersect_batch, every render kernel) runs this very test on the pairs its FP32 filters let
+ * through; this call is the filter-free yardstick for it and the call for a caller whose rays are f64. */
 int rtb200_intersect_batch_f64(rtb200_ctx* ctx, const double* ox, const double* oy, const double* oz, const double* dx,
                                const double* dy, const double* dz, const uint8_t* enabled, int64_t n,
                                int32_t* hit_index, double* hit_t);
@@ -244,6 +248,18 @@ int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode);
 
 /* Number of kernel launches this context has issued since creation (trace, resolve, intersect, probe). */
 int64_t rtb200_launch_count(rtb200_ctx* ctx);
+
+/* Self-check of the sweep's conservative FP32 filters, on the device, with the arithmetic the render kernels run.  The
+ * reference tests every (ray, sphere) pair with Sphere::hit_packed's discriminant (src/objects.rs:252-259); the sweeps run
+ * that test (in f64) only on pairs that pass two cheaper FP32 tests, which must therefore never reject a pair with
+ * discriminant >= 0.  This call brute-forces n_rays * per_ray adversarial pairs of the uploaded scene (rays aimed at sphere
+ * silhouettes with relative perturbations 1e-9 .. 1e-1, from camera_point (null: 13,2,3), from sphere surfaces and from
+ * far out on the largest sphere) and counts: out[0] pairs, [1] pairs with discriminant >= 0, [2] candidates of the 8-FLOP
+ * filter, [3] its FALSE NEGATIVES (must be 0), [4..6] candidates of the slab test per dropped axis, [7] its FALSE
+ * NEGATIVES over the three axes (must be 0), [8] reserved.  *min_slack (may be null) = the smallest filter value over
+ * discriminant >= 0 pairs in units of the proven margin (1 = no rounding error observed, 0 = margin used up). */
+int rtb200_filter_check(rtb200_ctx* ctx, uint64_t n_rays, int32_t per_ray, uint32_t seed, const double camera_point[3],
+                        uint64_t out[9], double* min_slack);
 
 /* K0: measures sustained FP32 FMA throughput (dependent-free FFMA chains on every SM) — the roofline
  * denominator for this path (the driver's MEASURED_PEAKS.json holds only HBM and BF16 figures).

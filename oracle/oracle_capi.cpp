@@ -1,7 +1,9 @@
 // oracle_capi.cpp — C entry points over rt_oracle.hpp for ctypes.  TEST INFRASTRUCTURE ONLY (see rt_oracle.hpp).
-// Plain arrays in, plain arrays out.  "_f32" entry points run the float instantiation (the GPU comparand),
-// "_f64" the reference-faithful double instantiation.  Scene/camera inputs are always double (the reference's
-// types are f64) and are cast to float exactly as the CUDA upload does ((float)x, round to nearest).
+// Plain arrays in, plain arrays out.  Every entry point that computes takes `use_f32`: 0 = the reference-faithful
+// double instantiation; 1 = MIXED, the GPU comparand (FP32 path state, closest-hit sweep in f64 on the f64 scene,
+// rt_oracle.hpp); 2 = pure FP32 (kept to measure what FP32 hit arithmetic costs against the reference).  Scene/camera
+// inputs are always double (the reference's types are f64) and are cast to float exactly as the CUDA upload does
+// ((float)x, round to nearest).
 #include "rt_oracle.hpp"
 
 #include <algorithm>
@@ -19,10 +21,15 @@ static bool g_both_roots = false;
 template <class R>
 Scene<R> make_scene(const double* spheres /*[n][4] cx cy cz r*/, const int32_t* sphere_material, int32_t n,
                     const int32_t* mat_kind, const int32_t* mat_hollow, const double* mat_albedo /*[m][3]*/,
-                    const double* mat_param, int32_t m) {
+                    const double* mat_param, int32_t m, bool mixed = false) {
     Scene<R> s;
     s.both_roots = g_both_roots;
     s.spheres.resize(n);
+    if (mixed) {
+        s.exact64.resize(n);
+        for (int32_t i = 0; i < n; i++)
+            s.exact64[i] = Sphere<double>{{spheres[4 * i + 0], spheres[4 * i + 1], spheres[4 * i + 2]}, spheres[4 * i + 3], 0};
+    }
     for (int32_t i = 0; i < n; i++) {
         s.spheres[i].center = {(R)spheres[4 * i + 0], (R)spheres[4 * i + 1], (R)spheres[4 * i + 2]};
         s.spheres[i].radius = (R)spheres[4 * i + 3];
@@ -140,7 +147,7 @@ void oracle_camera_get_ray(int32_t width, int32_t height, const double* cam18, i
 void oracle_intersect(const double* spheres, int32_t n_spheres, const double* rays, const int32_t* enabled, int64_t n_rays,
                       int32_t use_f32, int32_t* idx_out, double* t_out) {
     const int32_t kind = 0, hollow = 0; const double alb[3] = {0, 0, 0}, par = 0;
-    if (use_f32) intersect_impl(make_scene<float>(spheres, nullptr, n_spheres, &kind, &hollow, alb, &par, 1), rays, enabled, n_rays, idx_out, t_out);
+    if (use_f32) intersect_impl(make_scene<float>(spheres, nullptr, n_spheres, &kind, &hollow, alb, &par, 1, use_f32 == 1), rays, enabled, n_rays, idx_out, t_out);
     else intersect_impl(make_scene<double>(spheres, nullptr, n_spheres, &kind, &hollow, alb, &par, 1), rays, enabled, n_rays, idx_out, t_out);
 }
 
@@ -151,7 +158,7 @@ void oracle_hit_and_scatter(const double* sphere4, int32_t mat_kind, int32_t mat
     const int32_t mi = 0;
     auto run = [&](auto tag) {
         using R = decltype(tag);
-        Scene<R> sc = make_scene<R>(sphere4, &mi, 1, &mat_kind, &mat_hollow, albedo3, &param, 1);
+        Scene<R> sc = make_scene<R>(sphere4, &mi, 1, &mat_kind, &mat_hollow, albedo3, &param, 1, sizeof(R) == 4 && use_f32 == 1);
         Ray<R> r{{(R)ray6[0], (R)ray6[1], (R)ray6[2]}, {(R)ray6[3], (R)ray6[4], (R)ray6[5]}};
         SweepHit<R> h = sweep(sc, r);
         for (int i = 0; i < 18; i++) out18[i] = 0.0;
@@ -190,7 +197,7 @@ void oracle_render(const double* spheres, const int32_t* sphere_material, int32_
                    double* sum_out, uint8_t* rgb8_out, uint64_t* segments_out) {
     CameraD cd = make_camera(width, height, cam18);
     if (use_f32)
-        render_impl(make_scene<float>(spheres, sphere_material, n_spheres, mat_kind, mat_hollow, mat_albedo, mat_param, n_materials),
+        render_impl(make_scene<float>(spheres, sphere_material, n_spheres, mat_kind, mat_hollow, mat_albedo, mat_param, n_materials, use_f32 == 1),
                     cd, s0, s1, spp_total, depth, seed_lo, seed_hi, row0, row1, threads, sum_out, rgb8_out, segments_out);
     else
         render_impl(make_scene<double>(spheres, sphere_material, n_spheres, mat_kind, mat_hollow, mat_albedo, mat_param, n_materials),

@@ -15,7 +15,13 @@
 //
 // Every function cites the reference file:line it restates.  The code is templated on the scalar type:
 //   Real = double : reference-faithful arithmetic (the reference is f64 throughout, src/geometry.rs:9-13)
-//   Real = float  : the GPU comparand — same operation order, same FMA placement, IEEE sqrt/div.
+//   Real = float  : same operation order, same FMA placement, IEEE sqrt/div, in FP32 (the north_star's GPU arithmetic).
+//   Real = float with Scene::exact64 filled ("mixed", the GPU COMPARAND): the path state (rays, hit points, normals,
+//                   materials, colours) is FP32, but the closest-hit sweep — Sphere::hit_packed + PackedHitRecords::update —
+//                   runs in f64 on the f64 scene from the FP32-valued ray, and hands back the f64 root rounded once to
+//                   FP32.  This is what the CUDA kernels do (rt_kernels.cuh test_candidate): it keeps the intersection
+//                   inside the north_star's 1e-5 bar against the reference's f64 routine, which pure FP32 misses on the
+//                   1000-unit ground sphere (cancellation in the discriminant).
 // Compile with -ffp-contract=off so that the ONLY fused multiply-adds are the explicit std::fma calls,
 // which sit exactly where the reference calls mul_add (src/geometry.rs:435,467; src/objects.rs:257).
 //
@@ -173,7 +179,12 @@ template <class R> struct Material {
     R param;          // metal: fuzzy_factor (already clamped to <= 1, materials.rs:79-88); dielectric: index_of_refraction
 };
 template <class R> struct Sphere { V3<R> center; R radius; int32_t material; };
-template <class R> struct Scene { std::vector<Sphere<R>> spheres; std::vector<Material<R>> materials; bool both_roots = false; };
+template <class R> struct Scene {
+    std::vector<Sphere<R>> spheres;
+    std::vector<Material<R>> materials;
+    bool both_roots = false;
+    std::vector<Sphere<double>> exact64;   // mixed mode (R = float only): the scene at the reference's precision; empty = sweep in R
+};
 
 template <class R> struct Ray { V3<R> o, d; };   // src/ray.rs:5-18 — direction stored as given, never normalised
 
@@ -266,20 +277,20 @@ template <class R> inline R sphere_discriminant(const Sphere<R>& s, const Ray<R>
 // scene.both_roots (NOT the reference's live path; rtb200's RTB200_HIT_BOTH_ROOTS option): the rule of the scalar
 // Sphere::hit (src/objects.rs:227-234) inside the packed arithmetic — when root1 is outside the range, root2 (:271) is
 // tried.
-template <class R> inline SweepHit<R> sweep(const Scene<R>& scene, const Ray<R>& ray, bool enabled = true) {
+template <class R> inline SweepHit<R> sweep_spheres(const std::vector<Sphere<R>>& spheres, bool both_roots, const Ray<R>& ray, bool enabled) {
     const R T_MIN = (R)0.001;
     const R INF = std::numeric_limits<R>::infinity();
     SweepHit<R> best{false, -1, INF};                              // PackedHitRecords::default, objects.rs:121-134
-    const int32_t n = (int32_t)scene.spheres.size();
+    const int32_t n = (int32_t)spheres.size();
     for (int32_t i = 0; i < n; i++) {
         R half_b, a;
-        R disc = sphere_discriminant(scene.spheres[i], ray, half_b, a);
+        R disc = sphere_discriminant(spheres[i], ray, half_b, a);
         R inv_a = (R)1.0 / a;                                      // :254
         if (disc >= (R)0.0 && enabled) {                           // :259
             R sq = std::sqrt(disc);                                // :263
             R root1 = (-half_b - sq) * inv_a;                      // :270
             bool valid = (root1 >= T_MIN) && (root1 < INF) && enabled;   // :272-277
-            if (!valid && scene.both_roots) {                      // scalar rule, :230-234
+            if (!valid && both_roots) {                            // scalar rule, :230-234
                 root1 = (-half_b + sq) * inv_a;                    // :271
                 valid = (root1 >= T_MIN) && (root1 < INF) && enabled;
             }
@@ -289,6 +300,17 @@ template <class R> inline SweepHit<R> sweep(const Scene<R>& scene, const Ray<R>&
         }
     }
     return best;
+}
+
+// The scene's sweep.  Mixed mode (exact64 filled): the ray's FP32 values are promoted exactly, the routine above runs in
+// f64 over the f64 scene, and the winning root is rounded once to R.
+template <class R> inline SweepHit<R> sweep(const Scene<R>& scene, const Ray<R>& ray, bool enabled = true) {
+    if (!scene.exact64.empty()) {
+        const Ray<double> r64{{(double)ray.o.x, (double)ray.o.y, (double)ray.o.z}, {(double)ray.d.x, (double)ray.d.y, (double)ray.d.z}};
+        const SweepHit<double> h = sweep_spheres<double>(scene.exact64, scene.both_roots, r64, enabled);
+        return SweepHit<R>{h.hit, h.index, (R)h.t};
+    }
+    return sweep_spheres<R>(scene.spheres, scene.both_roots, ray, enabled);
 }
 
 // PackedHitRecords::finalize (src/objects.rs:157-162) for the winning sphere.  The un-normalised normal is

@@ -77,6 +77,7 @@ SYMBOLS = {
     "rtb200_set_hit_mode": (C.c_int32, [_P, C.c_int32]),
     "rtb200_set_progress": (C.c_int32, [_P, C.c_void_p, C.c_void_p, C.c_int32]),
     "rtb200_fp32_peak": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "rtb200_filter_check": (C.c_int, [_P, C.c_uint64, C.c_int32, C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_uint64), C.POINTER(C.c_double)]),
 }
 
 

@@ -25,14 +25,14 @@ constexpr int SWEEP_BLOCK = 32;          // spheres per candidate-mask word
 constexpr int LIST_CAP = 6;              // deferred candidate-mask entries per ray before a forced drain (general case)
 constexpr int LIST_CAP_SMALL = 16;       // scenes of <= 512 spheres: one entry per 32-block always fits, no overflow check
 constexpr int LIST_CAP_V = 8;            // parameter-space variant (two rays per lane, path state in shared memory)
-constexpr float T_MIN = 0.001f;          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
 #define RTB_INF __int_as_float(0x7f800000)
 
 // ---- sphere staging ------------------------------------------------------------------------------------------
-// Two device arrays per scene, both in list order: the EXACT spheres float4 {cx, cy, cz, r*r} (global memory, read
-// only by the candidate re-test and by shading) and the FILTER spheres float4 {cx, cy, cz, k} (rt_filter.h), which
-// are what the sweep stages in shared memory.  `count` spheres are copied as they are (no padding: the sweep handles
-// the remainder of the last 32-block with a rolled loop).
+// Three device arrays per scene take part in the sweep, all in list order and padded to whole 32-blocks with never-hit
+// spheres: the FILTER spheres float4 {cx, cy, cz, k} (rt_filter.h), which the one-stage sweeps stage in shared memory
+// and stage 2 of the two-stage sweep reads per candidate; the stage-1 triples; and the EXACT spheres
+// double4 {cx, cy, cz, r*r} at the reference's own precision (the f64 values of the scene description, not their f32
+// roundings), read only by the exact candidate test below.  Shading reads the f32 centres float4 {cx, cy, cz, r*r}.
 __device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __restrict__ g_flt, int begin, int count) {
     for (int i = threadIdx.x; i < count; i += blockDim.x) s_sph[i] = __ldg(&g_flt[begin + i]);
 }
@@ -50,31 +50,55 @@ __device__ __forceinline__ ExactRay make_exact_ray(f3 o, f3 d, bool both_roots) 
 // The ray's half of the candidate filter; a = d.d as the sweep computes it (src/objects.rs:253).
 __device__ __forceinline__ FilterRay make_filter(f3 o, f3 d) { return make_filter_ray(o.x, o.y, o.z, d.x, d.y, d.z, plen2_3(d)); }
 
-// The discriminant of hit_packed in the reference's operation order (src/objects.rs:252-257):
-// 3 FADD (oc), FMUL + 2 FFMA (half_b), FMUL + 2 FFMA + FADD (c), FMUL + FFMA (disc) = 12 FP32 instructions, 17 FLOP.
-__device__ __forceinline__ float discriminant(const ExactRay& r, float a, float4 s, float& hb) {
-    float ocx = __fsub_rn(r.ox, s.x), ocy = __fsub_rn(r.oy, s.y), ocz = __fsub_rn(r.oz, s.z);       // :252
-    hb = __fmaf_rn(ocz, r.dz, __fmaf_rn(ocy, r.dy, __fmul_rn(ocx, r.dx)));                          // :255
-    float cc = __fsub_rn(__fmaf_rn(ocz, ocz, __fmaf_rn(ocy, ocy, __fmul_rn(ocx, ocx))), s.w);       // :256
-    return __fmaf_rn(hb, hb, -__fmul_rn(a, cc));                                                    // :257
+// ---- the exact candidate test: Sphere::hit_packed at the reference's precision -----------------------------------------
+// The reference is f64 throughout (src/geometry.rs:9-13).  The all-pairs passes of the sweep are FP32 filters with no
+// false negatives; what survives them (~1 % of the pairs) is tested HERE with the reference's own arithmetic in its own
+// scalar type: the FP32 ray of the path state promoted to f64 (exact), the f64 spheres of the scene description, the
+// reference's operation order and mul_add sites (src/objects.rs:252-257,263,270-277), IEEE sqrt and division, and the
+// `<=` closest-hit update on the f64 root (:141).  For a given (FP32-valued) ray the sweep therefore returns the object
+// index of the reference's f64 routine exactly and its hit distance rounded once to FP32 (<= 6e-8 relative): the
+// north_star's intersection bar (index exact, t within 1e-5 of the packed-SIMD hit routine) holds on the render path, not
+// only on a probe.  An FP32 version of this test (round 1) cancelled on the 1000-unit ground sphere: 77 % of hits inside
+// 1e-5, worst 6e-4.  B200 issues FP64 at half the FP32 rate and this code sees ~1 % of the pairs.
+struct ExactRay64 { double ox, oy, oz, dx, dy, dz, a, inv_a; };
+
+__device__ __forceinline__ ExactRay64 promote_ray(const ExactRay& r) {
+    ExactRay64 e;
+    e.ox = (double)r.ox; e.oy = (double)r.oy; e.oz = (double)r.oz;
+    e.dx = (double)r.dx; e.dy = (double)r.dy; e.dz = (double)r.dz;
+    e.a = __fma_rn(e.dz, e.dz, __fma_rn(e.dy, e.dy, __dmul_rn(e.dx, e.dx)));                        // src/objects.rs:253
+    e.inv_a = __ddiv_rn(1.0, e.a);                                                                  // :254
+    return e;
 }
 
-// Exact per-candidate test: the body of hit_packed's `if discriminant_positive.any()` block for one lane
-// (src/objects.rs:262-288) followed by PackedHitRecords::update (:140-147).
-__device__ __forceinline__ void test_candidate(const ExactRay& r, float a, float inv_a, float4 s, int index, float& best_t, int& best_i) {
-    float hb;
-    float disc = discriminant(r, a, s, hb);
-    if (disc >= 0.0f) {                                                                            // :259
-        float sq = __fsqrt_rn(disc);                                                               // :263
-        float root1 = __fmul_rn(__fsub_rn(-hb, sq), inv_a);                                        // :270
-        bool valid = (root1 >= T_MIN) && (root1 < RTB_INF);                                        // :272-277 (near root only, F4)
-        if (!valid && r.both_roots) {                                                              // scalar Sphere::hit, :230-234
-            root1 = __fmul_rn(__fadd_rn(-hb, sq), inv_a);                                          // :271
-            valid = (root1 >= T_MIN) && (root1 < RTB_INF);
+// The body of hit_packed for one lane (src/objects.rs:252-288) followed by PackedHitRecords::update (:140-147).
+// s = {cx, cy, cz, r*r} (radius.powi(2) evaluated in f64 on the host, :256).
+__device__ __forceinline__ double exact_discriminant(const ExactRay64& r, double4 s, double& hb) {
+    const double ocx = __dsub_rn(r.ox, s.x), ocy = __dsub_rn(r.oy, s.y), ocz = __dsub_rn(r.oz, s.z);   // :252
+    hb = __fma_rn(ocz, r.dz, __fma_rn(ocy, r.dy, __dmul_rn(ocx, r.dx)));                               // :255
+    const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), s.w);     // :256
+    return __fma_rn(hb, hb, -__dmul_rn(r.a, cc));                                                     // :257
+}
+__device__ __forceinline__ void test_candidate(const ExactRay64& r, bool both_roots, double4 s, int index, double& best_t, int& best_i) {
+    double hb;
+    const double disc = exact_discriminant(r, s, hb);
+    if (disc >= 0.0) {                                                                             // :259
+        const double T_MIN_D = 0.001, INF_D = __longlong_as_double(0x7ff0000000000000LL);          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
+        const double sq = __dsqrt_rn(disc);                                                        // :263
+        double root1 = __dmul_rn(__dsub_rn(-hb, sq), r.inv_a);                                     // :270
+        bool valid = (root1 >= T_MIN_D) && (root1 < INF_D);                                        // :272-277 (near root only, F4)
+        if (!valid && both_roots) {                                                                // scalar Sphere::hit, :230-234
+            root1 = __dmul_rn(__dadd_rn(-hb, sq), r.inv_a);                                        // :271
+            valid = (root1 >= T_MIN_D) && (root1 < INF_D);
         }
         if (valid && root1 <= best_t) { best_t = root1; best_i = index; }                          // :141 (`<=`: last wins, F5)
     }
 }
+__device__ __forceinline__ double4 load_exact(const double4* __restrict__ p) {                     // 32 bytes, one sector
+    const double2 lo = __ldg(reinterpret_cast<const double2*>(p)), hi = __ldg(reinterpret_cast<const double2*>(p) + 1);
+    return make_double4(lo.x, lo.y, hi.x, hi.y);
+}
+#define RTB_INF_D __longlong_as_double(0x7ff0000000000000LL)
 
 // Where the sweep reads its warp-uniform sphere operand from.
 //   SmemSpheres : the staged shared-memory array (LDS.128 -> 4 registers; a chain FFMA then reads 3 registers, which
@@ -95,11 +119,10 @@ struct RegisterRays {
 
 // Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 filter values (bit
 // 31 = first sphere of the block, set = not a candidate), index of the block's first sphere in the staged array}.
-// g_exact = the exact spheres of the staged range (global memory, L1-resident).
-__device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_exact, int index_base, const uint2* list, int list_stride, int& n_list,
-                                                 const ExactRay& r, float& best_t, int& best_i) {
-    const float a = plen2_3(mk3(r.dx, r.dy, r.dz));                                                // :253
-    const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
+// g_exact = the exact (f64) spheres of the staged range (global memory, L1-resident).
+__device__ __forceinline__ void drain_candidates(const double4* __restrict__ g_exact, int index_base, const uint2* list, int list_stride, int& n_list,
+                                                 const ExactRay& r32, double& best_t, int& best_i) {
+    const ExactRay64 r = promote_ray(r32);
     int e = 0;
     uint32_t cand = 0;
     int cbase = 0;
@@ -114,7 +137,7 @@ __device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_ex
         int j = __clz(cand);
         cand &= ~(0x80000000u >> j);
         int local = cbase + j;
-        test_candidate(r, a, inv_a, __ldg(&g_exact[local]), index_base + local, best_t, best_i);
+        test_candidate(r, r32.both_roots, load_exact(&g_exact[local]), index_base + local, best_t, best_i);
     }
     n_list = 0;
 }
@@ -130,9 +153,9 @@ __device__ __forceinline__ void drain_candidates(const float4* __restrict__ g_ex
 // list layout: entry e of ray r of this thread at list[(r * CAP + e) * list_stride].  CAP >= number of 32-blocks
 // (CHECKED = false) removes the overflow test from the per-block path.
 template <int RAYS, int CAP, bool CHECKED, class SphSrc, class RaySrc>
-__device__ __forceinline__ void sweep_spheres(const SphSrc& sph, const RaySrc& rays, const float4* __restrict__ g_exact, int count,
+__device__ __forceinline__ void sweep_spheres(const SphSrc& sph, const RaySrc& rays, const double4* __restrict__ g_exact, int count,
                                               int index_base, uint2* list, int list_stride, const FilterRay (&f)[RAYS],
-                                              float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+                                              double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     int n_list[RAYS];
 #pragma unroll
     for (int r = 0; r < RAYS; r++) n_list[r] = 0;
@@ -214,8 +237,8 @@ __device__ __forceinline__ void sweep_spheres(const SphSrc& sph, const RaySrc& r
 // walks the set bits in block order: a stored mask is re-tested bit by bit, a block beyond the CAP-th (rare) is
 // re-tested whole.  Exact tests therefore run in sweep order, as PackedHitRecords::update needs (`<=`: last wins).
 template <int RAYS, int CAP, class SphSrc, class RaySrc>
-__device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const RaySrc& rays, const float4* __restrict__ g_exact, int count,
-                                                     uint32_t* list, int list_stride, const FilterRay (&f)[RAYS], float (&best_t)[RAYS],
+__device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const RaySrc& rays, const double4* __restrict__ g_exact, int count,
+                                                     uint32_t* list, int list_stride, const FilterRay (&f)[RAYS], double (&best_t)[RAYS],
                                                      int (&best_i)[RAYS]) {
     uint32_t blocks[RAYS];
     int n_list[RAYS];
@@ -278,9 +301,8 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
 #pragma unroll
     for (int r = 0; r < RAYS; r++) {
         if (blocks[r] == 0u) continue;
-        const ExactRay ray = rays.load(r);
-        const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                      // src/objects.rs:253
-        const float inv_a = __fdiv_rn(1.0f, a);                                                    // :254
+        const ExactRay ray32 = rays.load(r);
+        const ExactRay64 ray = promote_ray(ray32);
         const uint32_t fill = rem > 0 ? (0xffffffffu >> rem) : 0u;                                  // never-candidates of a partial last block
         uint32_t todo = blocks[r];
         int e = 0;
@@ -293,7 +315,7 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
             while (cand) {
                 const int j = __clz(cand);
                 cand &= ~(0x80000000u >> j);
-                test_candidate(ray, a, inv_a, __ldg(&g_exact[cbase + j]), cbase + j, best_t[r], best_i[r]);
+                test_candidate(ray, ray32.both_roots, load_exact(&g_exact[cbase + j]), cbase + j, best_t[r], best_i[r]);
             }
         }
     }
@@ -305,8 +327,7 @@ __device__ __forceinline__ void sweep_spheres_bitmap(const SphSrc& sph, const Ra
 // ever takes warp-uniform VALUES, at lane-dependent TIMES, ptxas 12.9 parked it in a uniform register which partial
 // warps then advanced: lanes skipped blocks.)  The device arrays are padded to whole blocks with never-hit spheres, so
 // a padding bit that slips through stage 1 (NaN ray) is harmless.
-struct Best { float t; int i; };
-struct alignas(32) SpherePair { float4 filter, exact; };   // what stages 2 and 3 read for one sphere: one 32-byte record
+struct Best { double t; int i; };                          // the running closest hit: the f64 root and its object index
 #ifndef RTB_REFINE_INLINE
 #define RTB_REFINE_INLINE __forceinline__   // two inlined copies (one per ray of the lane) beat one out-of-line copy by 5 %
 #endif
@@ -330,17 +351,16 @@ __device__ __forceinline__ bool walk_next(const uint32_t* masks_r, int stride, u
 }
 
 __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
-                                          const SpherePair* __restrict__ g_pairs, FilterRay f, ExactRay ray, Best best) {
+                                          const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, FilterRay f, ExactRay ray32,
+                                          Best best) {
     if (todo == 0u) return best;
-    const float a = plen2_3(mk3(ray.dx, ray.dy, ray.dz));                                          // src/objects.rs:253
-    const float inv_a = __fdiv_rn(1.0f, a);                                                        // :254
+    const ExactRay64 ray = promote_ray(ray32);
     uint32_t cand = 0;
     int last = 0, idx = 0;                                 // last = index of the current block's sphere 31
     while (walk_next(masks_r, stride, todo, cand, last, first_sphere, idx)) {
-        const SpherePair* rec = g_pairs + idx;             // {filter, exact} of sphere idx
-        const float4 fs = __ldg(&rec->filter);
-        const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2
-        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, a, inv_a, __ldg(&rec->exact), idx, best.t, best.i);   // stage 3
+        const float4 fs = __ldg(&g_filter[idx]);
+        const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2 (FP32, conservative)
+        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, ray32.both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);   // stage 3 (f64, exact)
     }
     return best;
 }
@@ -387,9 +407,9 @@ struct SmemSlab {
 };
 
 template <int RAYS, class S1, class RaySrc>
-__device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const SpherePair* __restrict__ g_pairs, int count,
-                                                uint32_t* masks, int stride,
-                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS], int (&best_i)[RAYS]) {
+__device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const float4* __restrict__ g_filter,
+                                                const double4* __restrict__ g_exact, int count, uint32_t* masks, int stride,
+                                                const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
         const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
@@ -414,7 +434,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -439,9 +459,9 @@ constexpr int STREAM_CHUNK_F4 = 8 * SWEEP_BLOCK * 3 / 4;     // float4 per chunk
 
 template <int RAYS, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float4* __restrict__ g_s1, unsigned lane, const RaySrc& rays,
-                                                       const SpherePair* __restrict__ g_pairs, int n_padded, uint32_t* masks, int stride,
-                                                       const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], float (&best_t)[RAYS],
-                                                       int (&best_i)[RAYS]) {
+                                                       const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, int n_padded,
+                                                       uint32_t* masks, int stride, const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS],
+                                                       double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = n_padded / SWEEP_BLOCK;              // the device arrays are padded to whole blocks
     const int n_chunks = (n_blocks + 7) / 8;
     auto issue = [&](int c) {                                 // chunk c -> half (c & 1) of the warp's buffer, one commit group
@@ -479,7 +499,7 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_pairs, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -490,7 +510,7 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
 // ---- K1 ----------------------------------------------------------------------------------------------------------
 // One thread per ray; spheres streamed through shared memory in tiles of `tile` (multiple of SWEEP_BLOCK).
 // dynamic smem: tile float4 + LIST_CAP * blockDim uint2.
-__global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restrict__ g_sph, const float4* __restrict__ g_flt, int n_spheres, int tile,
+__global__ void __launch_bounds__(256) k_intersect_batch(const double4* __restrict__ g_sph, const float4* __restrict__ g_flt, int n_spheres, int tile,
                                                          const float* __restrict__ ox, const float* __restrict__ oy,
                                                          const float* __restrict__ oz, const float* __restrict__ dx,
                                                          const float* __restrict__ dy, const float* __restrict__ dz,
@@ -505,7 +525,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     if (live) { o = mk3(ox[i], oy[i], oz[i]); d = mk3(dx[i], dy[i], dz[i]); }
     ExactRay ray[1] = {make_exact_ray(o, d, both_roots != 0)};
     FilterRay flt[1] = {make_filter(o, d)};
-    float best_t[1] = {RTB_INF};                               // PackedHitRecords::default, src/objects.rs:121-134
+    double best_t[1] = {RTB_INF_D};                            // PackedHitRecords::default, src/objects.rs:121-134
     int best_i[1] = {-1};
     for (int begin = 0; begin < n_spheres; begin += tile) {
         int count = min(tile, n_spheres - begin);
@@ -517,18 +537,18 @@ __global__ void __launch_bounds__(256) k_intersect_batch(const float4* __restric
     if (live) {
         bool en = enabled ? enabled[i] != 0 : true;            // rays.enabled(), src/objects.rs:259,277
         hit_index[i] = en ? best_i[0] : -1;
-        hit_t[i] = (en && best_i[0] >= 0) ? best_t[0] : RTB_INF;
+        hit_t[i] = (en && best_i[0] >= 0) ? __double2float_rn(best_t[0]) : RTB_INF;   // the f64 root, rounded once
     }
 }
 
 // ---- K1d: the reference's routine at the reference's precision ---------------------------------------------------------
 // Sphere::hit_packed + PackedHitRecords::update (src/objects.rs:249-290, :140-155) for one ray per thread in f64 — the
-// reference's own scalar type (src/geometry.rs:9-13) — over f64 spheres {cx, cy, cz, r} in list order, every pair, no
+// reference's own scalar type (src/geometry.rs:9-13) — over f64 spheres {cx, cy, cz, r*r} in list order, EVERY pair, no
 // filter.  Same operation order and FMA sites as the reference (mul_add at src/geometry.rs:435,467 and src/objects.rs:257),
-// IEEE sqrt and division: the result equals the f64 routine bit for bit.  It is the PROBE that says how far the FP32
-// production sweep is from the reference on given rays (index equal; t to ~1e-6 median, 6e-4 worst on the ground
-// sphere), and the way to get f64 hit distances where a caller needs them; the render path stays FP32 (north_star).
-// Spheres go through shared memory in tiles of 256 (8 KB).
+// IEEE sqrt and division: the result equals the f64 routine bit for bit, for f64-valued rays.  The production sweep
+// (K1, every K2 variant) runs the same test only on the candidates its FP32 filters let through; this kernel is the
+// filter-free yardstick the tests hold it against (same index, t equal after one rounding to FP32), and the call for a
+// caller whose rays are f64.  Spheres go through shared memory in tiles of 256 (8 KB).
 __global__ void __launch_bounds__(256) k_intersect_batch_f64(const double4* __restrict__ g_sph, int n_spheres, const double* __restrict__ ox,
                                                              const double* __restrict__ oy, const double* __restrict__ oz,
                                                              const double* __restrict__ dx, const double* __restrict__ dy,
@@ -553,7 +573,7 @@ __global__ void __launch_bounds__(256) k_intersect_batch_f64(const double4* __re
             const double4 sp = s_sph[j];
             const double ocx = __dsub_rn(rox, sp.x), ocy = __dsub_rn(roy, sp.y), ocz = __dsub_rn(roz, sp.z);          // :252
             const double hb = __fma_rn(ocz, rdz, __fma_rn(ocy, rdy, __dmul_rn(ocx, rdx)));                            // :255
-            const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), __dmul_rn(sp.w, sp.w));   // :256
+            const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), sp.w);   // :256 (sp.w = radius.powi(2), host f64)
             const double disc = __fma_rn(hb, hb, -__dmul_rn(a, cc));                                                  // :257
             if (disc >= 0.0) {                                                                                        // :259
                 const double sq = __dsqrt_rn(disc);                                                                   // :263
@@ -577,9 +597,9 @@ __global__ void __launch_bounds__(256) k_intersect_batch_f64(const double4* __re
 // ---- K2 ----------------------------------------------------------------------------------------------------------
 struct TraceParams {
     DeviceCamera cam;
-    const float4* spheres;        // exact: {cx,cy,cz,r*r}
-    const float4* filter;         // candidate filter: {cx,cy,cz,k} (rt_filter.h)
-    const float4* pairs;          // {filter, exact} interleaved per sphere: what stages 2 and 3 of the two-stage sweep read
+    const float4* spheres;        // FP32 {cx,cy,cz,r*r}: shading (finalize_hit)
+    const float4* filter;         // candidate filter: {cx,cy,cz,k} (rt_filter.h): the one-stage sweeps, stage 2 of the two-stage sweep
+    const double4* exact;         // f64 {cx,cy,cz,r*r}: the exact candidate test (test_candidate)
     const float4* mat;            // per sphere {albedo rgb, param}
     const int* mat_kind;          // per sphere kind | hollow<<8
     int n_spheres;
@@ -900,15 +920,18 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         // the closest-hit sweep (all lanes; a slot without a path sweeps its stale ray and the result is ignored)
         ExactRay ray[RAYS];
         FilterRay flt[RAYS];
+        double bt[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
             flt[r] = make_filter(slot[r].o, slot[r].d);
-            best_t[r] = RTB_INF;                               // PackedHitRecords::default, src/objects.rs:121-134
+            bt[r] = RTB_INF_D;                                 // PackedHitRecords::default, src/objects.rs:121-134
             best_i[r] = -1;
         }
-        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(SmemSpheres{s_sph}, RegisterRays{ray}, P.spheres, P.n_spheres, 0, list, THREADS, flt,
-                                                         best_t, best_i);
+        sweep_spheres<RAYS, CAP, (CAP < LIST_CAP_SMALL)>(SmemSpheres{s_sph}, RegisterRays{ray}, P.exact, P.n_spheres, 0, list, THREADS, flt,
+                                                         bt, best_i);
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);   // the f64 root, rounded once for the FP32 path state
         swept = true;
     }
     flush_counters(P, n_paths, n_segments, lane);
@@ -959,17 +982,19 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         ExactRay ray[RAYS];
         FilterRay flt[RAYS];
         SlabRay slab[RAYS];
+        double bt[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
             flt[r] = make_filter(slot[r].o, slot[r].d);
             slab[r] = make_slab_ray(slot[r].o.x, slot[r].o.y, slot[r].o.z, slot[r].d.x, slot[r].d.y, slot[r].d.z, plen2_3(slot[r].d), PV.up_axis,
                                     PV.rp_min);
-            best_t[r] = RTB_INF;
+            bt[r] = RTB_INF_D;
             best_i[r] = -1;
         }
-        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, masks, THREADS, slab,
-                              flt, best_t, best_i);
+        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, P.filter, P.exact, P.n_spheres, masks, THREADS, slab, flt, bt, best_i);
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
     }
     flush_counters(P, n_paths, n_segments, lane);
@@ -1016,17 +1041,19 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
         ExactRay ray[RAYS];
         FilterRay flt[RAYS];
         SlabRay slab[RAYS];
+        double bt[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             ray[r] = make_exact_ray(slot[r].o, slot[r].d, P.both_roots != 0);
             flt[r] = make_filter(slot[r].o, slot[r].d);
             slab[r] = make_slab_ray(slot[r].o.x, slot[r].o.y, slot[r].o.z, slot[r].d.x, slot[r].d.y, slot[r].d.z, plen2_3(slot[r].d), PV.up_axis,
                                     PV.rp_min);
-            best_t[r] = RTB_INF;
+            bt[r] = RTB_INF_D;
             best_i[r] = -1;
         }
-        sweep_two_stage_stream<RAYS>(wbuf, PV.s1, lane, RegisterRays{ray}, reinterpret_cast<const SpherePair*>(P.pairs), PV.n_padded, masks, THREADS,
-                                     slab, flt, best_t, best_i);
+        sweep_two_stage_stream<RAYS>(wbuf, PV.s1, lane, RegisterRays{ray}, P.filter, P.exact, PV.n_padded, masks, THREADS, slab, flt, bt, best_i);
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
     }
     flush_counters(P, n_paths, n_segments, lane);
@@ -1113,12 +1140,12 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             continue;
         }
         FilterRay flt[RAYS];
-        float best_t[RAYS];
+        double best_t[RAYS];
         int best_i[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             flt[r] = make_filter(mk3(F(0, r), F(1, r), F(2, r)), mk3(F(3, r), F(4, r), F(5, r)));
-            best_t[r] = RTB_INF;
+            best_t[r] = RTB_INF_D;
             best_i[r] = -1;
         }
         if constexpr (PV_T::two_stage) {
@@ -1128,16 +1155,16 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             if constexpr (PV_T::s1_smem)
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
             else
-                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, reinterpret_cast<const SpherePair*>(P.pairs), P.n_spheres, list, THREADS, slab,
+                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.n_spheres, list, THREADS, slab,
                                       flt, best_t, best_i);
         } else {
-            sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.spheres, P.n_spheres, list, THREADS,
+            sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.exact, P.n_spheres, list, THREADS,
                                             flt, best_t, best_i);
         }
 #pragma unroll
-        for (int r = 0; r < RAYS; r++) { W(15, r) = __float_as_uint(best_t[r]); W(16, r) = (uint32_t)best_i[r]; }
+        for (int r = 0; r < RAYS; r++) { W(15, r) = __float_as_uint(__double2float_rn(best_t[r])); W(16, r) = (uint32_t)best_i[r]; }   // the f64 root, rounded once
         swept = true;
     }
     RTB_TL_EXIT(lane);
@@ -1231,6 +1258,122 @@ __global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ P
     } else {
         for (int k = 0; k < 3 * n; k++) rgb8[p0 * 3 + k] = (uint8_t)b[k];
     }
+}
+
+// ---- filter self-check: the conservative filters against the exact test, ON THE DEVICE --------------------------------
+// The parity of every sweep rests on two FP32 filters never rejecting a pair the exact (f64) test accepts.  This kernel
+// brute-forces that property with the arithmetic that actually runs: the device builds of make_filter / make_slab_ray
+// (approximate rsqrtf included) / filter_value / slab_value and exact_discriminant, on adversarial pairs of the UPLOADED
+// scene — rays aimed at a sphere's silhouette with relative perturbations 1e-9 .. 1e-1 to either side, from a camera
+// point, from points on other spheres' surfaces (bounce rays) and from far out on the largest sphere, directions of
+// length 0.1 .. 2 (the reference never normalises); each ray is tested against the aimed-at sphere and
+// `per_ray - 1` random others, for the slab test along all three axes.
+// out: [0] pairs, [1] exact-positive pairs (disc >= 0), [2] filter candidates, [3] filter FALSE NEGATIVES,
+//      [4..6] slab candidates per dropped axis, [7] slab FALSE NEGATIVES, [8] min over exact-positive pairs of
+//      filter value / margin, as float bits in the low word (atomicMin on the bit pattern of a non-negative float).
+struct FilterCheckArgs {
+    const float4* spheres; const float4* filter; const float* slab; const double4* exact;
+    int n_spheres; float rp_min; int largest;      // index of the sphere with the largest radius ("ground")
+    float cam[3];
+    unsigned long long n_rays; int per_ray; uint32_t seed;
+    unsigned long long* out;
+};
+
+__global__ void __launch_bounds__(256) k_filter_check(const FilterCheckArgs A) {
+    unsigned long long cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    float min_slack = 3.0e38f;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long ray_id = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; ray_id < A.n_rays; ray_id += stride) {
+        uint32_t ctr = 0;
+        auto rnd = [&]() { return philox4x32_10((uint32_t)ray_id, (uint32_t)(ray_id >> 32), ctr++, 0x51f7u, A.seed, 0x2545f491u); };
+        auto u01d = [](uint32_t x) { return ((double)x + 0.5) * (1.0 / 4294967296.0); };
+        auto unit_rand = [&](double v[3]) {
+            const uint4 q = rnd();
+            const double z = 1.0 - 2.0 * u01d(q.x), rr = sqrt(fmax(0.0, 1.0 - z * z)), ph = 6.283185307179586 * u01d(q.y);
+            v[0] = rr * cos(ph); v[1] = rr * sin(ph); v[2] = z;
+        };
+        // ---- origin (f32-valued, as the path state is)
+        const uint4 q0 = rnd();
+        const double pick = u01d(q0.x);
+        double o[3];
+        if (pick < 0.25) { o[0] = A.cam[0]; o[1] = A.cam[1]; o[2] = A.cam[2]; }
+        else {
+            const int bi = pick < 0.45 ? A.largest : (int)(q0.y % (uint32_t)A.n_spheres);
+            const float4 b = A.spheres[bi];
+            const double br = sqrt(fmax(0.0, (double)b.w));
+            double nn[3]; unit_rand(nn);
+            if (bi == A.largest && pick < 0.45) {                      // near the "top" of the ground sphere, out to 0.6 radii
+                const double rad = br * pow(10.0, -4.0 + 3.8 * u01d(q0.z)), ang = 6.283185307179586 * u01d(q0.w);
+                nn[0] = rad * cos(ang) / br; nn[2] = rad * sin(ang) / br; nn[1] = sqrt(fmax(0.0, 1.0 - nn[0] * nn[0] - nn[2] * nn[2]));
+            }
+            o[0] = b.x + nn[0] * br; o[1] = b.y + nn[1] * br; o[2] = b.z + nn[2] * br;
+        }
+        const float of[3] = {(float)o[0], (float)o[1], (float)o[2]};
+        // ---- the aimed-at sphere and a near-silhouette direction
+        const uint4 q1 = rnd();
+        const int ti = (int)(q1.x % (uint32_t)A.n_spheres);
+        const double4 ts = A.exact[ti];
+        const double tr = sqrt(fmax(0.0, ts.w));
+        const double oc[3] = {ts.x - (double)of[0], ts.y - (double)of[1], ts.z - (double)of[2]};
+        const double L = sqrt(oc[0] * oc[0] + oc[1] * oc[1] + oc[2] * oc[2]);
+        double d[3];
+        bool aimed = false;
+        if (L > tr * (1.0 + 1e-9) && u01d(q1.y) < 0.9) {
+            double ax[3]; unit_rand(ax);
+            const double dp = (ax[0] * oc[0] + ax[1] * oc[1] + ax[2] * oc[2]) / (L * L);
+            for (int k = 0; k < 3; k++) ax[k] -= dp * oc[k];
+            const double al = sqrt(ax[0] * ax[0] + ax[1] * ax[1] + ax[2] * ax[2]);
+            if (al > 1e-9) {
+                const double eps = pow(10.0, -9.0 + 8.0 * u01d(q1.z)) * ((q1.w & 1u) ? -1.0 : 1.0);
+                const double theta = asin(tr / L) * (1.0 + eps);
+                for (int k = 0; k < 3; k++) d[k] = cos(theta) * oc[k] / L + sin(theta) * ax[k] / al;
+                aimed = true;
+            }
+        }
+        if (!aimed) unit_rand(d);
+        const double scale = 0.1 + 1.9 * u01d(q1.w);
+        const f3 ro = mk3(of[0], of[1], of[2]), rd = mk3((float)(d[0] * scale), (float)(d[1] * scale), (float)(d[2] * scale));
+        // ---- what the sweeps compute per ray
+        const FilterRay fr = make_filter(ro, rd);
+        SlabRay sr[3];
+#pragma unroll
+        for (int up = 0; up < 3; up++) sr[up] = make_slab_ray(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z, plen2_3(rd), up, A.rp_min);
+        const ExactRay64 er = promote_ray(make_exact_ray(ro, rd, false));
+        const double o2 = (double)of[0] * of[0] + (double)of[1] * of[1] + (double)of[2] * of[2];
+        for (int rep = 0; rep < A.per_ray; rep++) {
+            int si = ti;
+            if (rep > 0) { const uint4 q = rnd(); si = (int)(q.x % (uint32_t)A.n_spheres); }
+            const float4 fs = A.filter[si];
+            const float4 sp = A.spheres[si];
+            const float rp = A.slab[3 * si + 2];
+            double hb;
+            const bool ref = exact_discriminant(er, A.exact[si], hb) >= 0.0;
+            const float qv = filter_value(fr, fs.x, fs.y, fs.z, fs.w);
+            const bool flag = !(__float_as_uint(qv) >> 31);
+            cnt[0]++; cnt[1] += ref; cnt[2] += flag; cnt[3] += (ref && !flag);
+            const float cc[3] = {sp.x, sp.y, sp.z};
+#pragma unroll
+            for (int up = 0; up < 3; up++) {
+                const int ia = up == 2 ? 0 : up + 1, ib = ia == 2 ? 0 : ia + 1;
+                const bool sflag = !(__float_as_uint(slab_value(sr[up], cc[ia], cc[ib], rp)) >> 31);
+                cnt[4 + up] += sflag;
+                cnt[7] += (ref && !sflag);
+            }
+            if (ref && flag) {
+                const double b = sqrt((double)sp.x * sp.x + (double)sp.y * sp.y + (double)sp.z * sp.z) + sqrt(fmax(0.0, (double)sp.w));
+                const double margin = (double)RTB_FILTER_MARGIN * (o2 + b * b);
+                if (margin > 0.0) min_slack = fminf(min_slack, (float)((double)qv / margin));
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        unsigned long long v = cnt[k];
+        for (int sh = 16; sh > 0; sh >>= 1) v += __shfl_xor_sync(0xffffffffu, v, sh);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&A.out[k], v);
+    }
+    for (int sh = 16; sh > 0; sh >>= 1) min_slack = fminf(min_slack, __shfl_xor_sync(0xffffffffu, min_slack, sh));
+    if ((threadIdx.x & 31) == 0) atomicMin(&A.out[8], (unsigned long long)__float_as_uint(fmaxf(min_slack, 0.0f)));
 }
 
 // ---- K0: FP32 FMA peak probe ----------------------------------------------------------------------------------------

@@ -68,10 +68,10 @@ struct rtb200_ctx {
     std::vector<unsigned char> h_params = std::vector<unsigned char>(sizeof(rtb::TraceParamsV<1024>) + 64);
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
-    double4* d_spheres64 = nullptr; size_t spheres64_count = 0;   // {cx, cy, cz, r} in f64, list order (rtb200_intersect_batch_f64)
-    float4* d_pairs = nullptr;                         // {filter, exact} interleaved per sphere (two-stage refine walk)
+    double4* d_exact = nullptr;                        // {cx, cy, cz, r*r} in f64, list order, padded: the exact candidate test of every sweep
     float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
     int n_padded = 32;
+    int largest_sphere = 0;                            // index of the sphere with the largest radius (rtb200_filter_check)
     int n_spheres = 0;
     // counters: [0] paths [1] segments [2] work counter
     unsigned long long* d_counters = nullptr;
@@ -156,7 +156,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const int n_samples = p->sample_end - p->sample_begin;
     rtb::TraceParams P;
     P.cam = device_camera(*cam);
-    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.pairs = ctx->d_pairs; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
+    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.exact = ctx->d_exact; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
     P.n_spheres = ctx->n_spheres;
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
@@ -346,7 +346,7 @@ int launch_intersect(rtb200_ctx* ctx, const float* ox, const float* oy, const fl
     }
     long long blocks = (n + threads - 1) / threads;
     if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
-    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_spheres, ctx->d_filter, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t,
+    rtb::k_intersect_batch<<<(unsigned)blocks, threads, smem, st>>>(ctx->d_exact, ctx->d_filter, ctx->n_spheres, tile, ox, oy, oz, dx, dy, dz, enabled, n, idx, t,
                                                                   ctx->hit_mode == RTB200_HIT_BOTH_ROOTS ? 1 : 0);
     CU_TRY(cudaGetLastError());
     ctx->launches++;
@@ -390,7 +390,7 @@ int rtb200_create(int32_t device, rtb200_ctx** out) {
 void rtb200_destroy(rtb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    cudaFree(c->d_scene); cudaFree(c->d_spheres64); cudaFree(c->d_counters);
+    cudaFree(c->d_scene); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->h_progress) cudaFreeHost(c->h_progress);
@@ -454,11 +454,12 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     if (scene->n_spheres < 0 || scene->n_materials < 0) return fail(RTB200_ERR_INVALID, "negative count");
     if (scene->n_spheres > 0 && (!scene->spheres || !scene->materials)) return fail(RTB200_ERR_INVALID, "null scene arrays");
     const int n = scene->n_spheres;
-    // device arrays are padded to whole 32-sphere blocks with spheres that can never be hit: exact {0,0,0,r^2 = -1}
-    // (discriminant < 0 for every ray), filter {0,0,0,k = +inf} (never a candidate)
+    // device arrays are padded to whole 32-sphere blocks with spheres that can never be hit: f64 exact {0,0,0,r^2 = NaN}
+    // (the discriminant is NaN, never >= 0, for every ray), filter {0,0,0,k = +inf} (never a candidate)
     const size_t cnt = (size_t)((n + 31) / 32 * 32 > 0 ? (n + 31) / 32 * 32 : 32);
     std::vector<float4> sph(cnt, make_float4(0.f, 0.f, 0.f, -1.0f)), flt(cnt, make_float4(0.f, 0.f, 0.f, INFINITY)),
         mat(cnt, make_float4(0.f, 0.f, 0.f, 0.f));
+    std::vector<double4> ex(cnt, make_double4(0.0, 0.0, 0.0, std::nan("")));
     std::vector<int> kind(cnt, 0);
     for (int i = 0; i < n; i++) {
         const rtb200_sphere& s = scene->spheres[i];
@@ -466,7 +467,8 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
             return fail(RTB200_ERR_INVALID, "sphere " + std::to_string(i) + " names material " + std::to_string(s.material) + " which does not exist");
         const rtb200_material& m = scene->materials[s.material];
         float r = (float)s.radius;
-        sph[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], r * r);   // radius.powi(2), src/objects.rs:256
+        sph[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], r * r);
+        ex[i] = make_double4(s.center[0], s.center[1], s.center[2], s.radius * s.radius);           // radius.powi(2) in f64, src/objects.rs:256
         // The f32 path squares coordinates: keep them far from overflow (the reference is f64 and has no such limit).
         if (!(std::fabs(sph[i].x) <= 1e15f && std::fabs(sph[i].y) <= 1e15f && std::fabs(sph[i].z) <= 1e15f && std::fabs(r) <= 1e15f))
             return fail(RTB200_ERR_INVALID, "sphere " + std::to_string(i) + ": centre/radius not finite or beyond 1e15 (f32 device path)");
@@ -515,45 +517,35 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         ctx->slab_pass = n > 0 ? pass / n : 1.0;
     }
     CU_TRY(cudaSetDevice(ctx->device));
-    // One device arena [spheres | filter | materials | kinds | stage-1 triples | {filter, exact} pairs], reused while it is large enough, filled by ONE copy.
-    const size_t bytes = cnt * (5 * sizeof(float4) + sizeof(int) + 3 * sizeof(float));
+    // One device arena [exact f64 | spheres | filter | materials | stage-1 triples | kinds], reused while it is large enough,
+    // filled by ONE copy (cnt is a multiple of 32, so every array starts 32-byte aligned).
+    const size_t off_sph = cnt * sizeof(double4), off_flt = off_sph + cnt * sizeof(float4), off_mat = off_flt + cnt * sizeof(float4),
+                 off_slab = off_mat + cnt * sizeof(float4), off_kind = off_slab + cnt * 3 * sizeof(float), bytes = off_kind + cnt * sizeof(int);
     if (ctx->scene_capacity < bytes) {
         cudaFree(ctx->d_scene);
         ctx->d_scene = nullptr; ctx->scene_capacity = 0;
-        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr; ctx->d_pairs = nullptr;
+        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr; ctx->d_exact = nullptr;
         CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
         ctx->scene_capacity = bytes;
     }
     std::vector<unsigned char> host(bytes);
-    std::memcpy(host.data(), sph.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + cnt * sizeof(float4), flt.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + 2 * cnt * sizeof(float4), mat.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + 3 * cnt * sizeof(float4), kind.data(), cnt * sizeof(int));
-    std::memcpy(host.data() + cnt * (3 * sizeof(float4) + sizeof(int)), ctx->h_slab.data(), cnt * 3 * sizeof(float));
-    {
-        float4* pr = reinterpret_cast<float4*>(host.data() + cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float)));
-        for (size_t i = 0; i < cnt; i++) { pr[2 * i] = flt[i]; pr[2 * i + 1] = sph[i]; }
-    }
+    std::memcpy(host.data(), ex.data(), cnt * sizeof(double4));
+    std::memcpy(host.data() + off_sph, sph.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + off_flt, flt.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + off_mat, mat.data(), cnt * sizeof(float4));
+    std::memcpy(host.data() + off_slab, ctx->h_slab.data(), cnt * 3 * sizeof(float));
+    std::memcpy(host.data() + off_kind, kind.data(), cnt * sizeof(int));
     CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
     unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
-    ctx->d_spheres = reinterpret_cast<float4*>(base);
-    ctx->d_filter = reinterpret_cast<float4*>(base + cnt * sizeof(float4));
-    ctx->d_mat = reinterpret_cast<float4*>(base + 2 * cnt * sizeof(float4));
-    ctx->d_mat_kind = reinterpret_cast<int*>(base + 3 * cnt * sizeof(float4));
-    ctx->d_slab = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int)));   // cnt % 32 == 0: 16-byte aligned
-    ctx->d_pairs = reinterpret_cast<float4*>(base + cnt * (3 * sizeof(float4) + sizeof(int) + 3 * sizeof(float)));
-    {   // the scene at the reference's precision, for the f64 probe
-        if (ctx->spheres64_count < (size_t)std::max(n, 1)) {
-            cudaFree(ctx->d_spheres64);
-            ctx->d_spheres64 = nullptr; ctx->spheres64_count = 0;
-            CU_TRY(cudaMalloc(&ctx->d_spheres64, (size_t)std::max(n, 1) * sizeof(double4)));
-            ctx->spheres64_count = (size_t)std::max(n, 1);
-        }
-        std::vector<double4> s64((size_t)n);
-        for (int i = 0; i < n; i++) s64[i] = make_double4(scene->spheres[i].center[0], scene->spheres[i].center[1], scene->spheres[i].center[2], scene->spheres[i].radius);
-        if (n > 0) CU_TRY(cudaMemcpy(ctx->d_spheres64, s64.data(), (size_t)n * sizeof(double4), cudaMemcpyHostToDevice));
-    }
+    ctx->d_exact = reinterpret_cast<double4*>(base);
+    ctx->d_spheres = reinterpret_cast<float4*>(base + off_sph);
+    ctx->d_filter = reinterpret_cast<float4*>(base + off_flt);
+    ctx->d_mat = reinterpret_cast<float4*>(base + off_mat);
+    ctx->d_slab = reinterpret_cast<float4*>(base + off_slab);
+    ctx->d_mat_kind = reinterpret_cast<int*>(base + off_kind);
     ctx->n_padded = (int)cnt;
+    ctx->largest_sphere = 0;
+    for (int i = 1; i < n; i++) if (sph[i].w > sph[ctx->largest_sphere].w) ctx->largest_sphere = i;
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);
     return RTB200_OK;
@@ -639,7 +631,7 @@ int rtb200_intersect_batch_f64(rtb200_ctx* ctx, const double* ox, const double* 
     }
     const long long blocks = ((long long)n + 255) / 256;
     if (blocks > 0x7fffffffLL) return fail(RTB200_ERR_INVALID, "too many rays in one batch");
-    rtb::k_intersect_batch_f64<<<(unsigned)blocks, 256, 0, 0>>>(ctx->d_spheres64, ctx->n_spheres, base, base + nn, base + 2 * nn, base + 3 * nn,
+    rtb::k_intersect_batch_f64<<<(unsigned)blocks, 256, 0, 0>>>(ctx->d_exact, ctx->n_spheres, base, base + nn, base + 2 * nn, base + 3 * nn,
                                                                base + 4 * nn, base + 5 * nn, d_en, n, d_idx, d_t,
                                                                ctx->hit_mode == RTB200_HIT_BOTH_ROOTS ? 1 : 0);
     CU_TRY(cudaGetLastError());
@@ -828,6 +820,36 @@ int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "null context");
     if (mode != RTB200_HIT_NEAR_ROOT && mode != RTB200_HIT_BOTH_ROOTS) return fail(RTB200_ERR_INVALID, "unknown hit mode " + std::to_string(mode));
     ctx->hit_mode = mode;
+    return RTB200_OK;
+}
+
+int rtb200_filter_check(rtb200_ctx* ctx, uint64_t n_rays, int32_t per_ray, uint32_t seed, const double camera_point[3], uint64_t out[9],
+                        double* min_slack) {
+    if (!ctx || !out) return fail(RTB200_ERR_INVALID, "null argument");
+    if (!ctx->d_spheres) return fail(RTB200_ERR_STATE, "no scene uploaded (call rtb200_upload_scene first)");
+    if (ctx->n_spheres < 1) return fail(RTB200_ERR_INVALID, "the scene has no spheres");
+    if (per_ray < 1 || per_ray > 64) return fail(RTB200_ERR_INVALID, "per_ray must be 1..64");
+    CU_TRY(cudaSetDevice(ctx->device));
+    unsigned long long* d_out = nullptr;
+    CU_TRY(cudaMalloc(&d_out, 9 * sizeof(unsigned long long)));
+    unsigned long long init[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0x7f7fffffull};
+    cudaError_t e = cudaMemcpy(d_out, init, sizeof init, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        rtb::FilterCheckArgs A;
+        A.spheres = ctx->d_spheres; A.filter = ctx->d_filter; A.slab = reinterpret_cast<const float*>(ctx->d_slab); A.exact = ctx->d_exact;
+        A.n_spheres = ctx->n_spheres; A.rp_min = ctx->slab_rp_min; A.largest = ctx->largest_sphere;
+        for (int k = 0; k < 3; k++) A.cam[k] = camera_point ? (float)camera_point[k] : (k == 0 ? 13.0f : k == 1 ? 2.0f : 3.0f);
+        A.n_rays = n_rays; A.per_ray = per_ray; A.seed = seed; A.out = d_out;
+        rtb::k_filter_check<<<ctx->prop.multiProcessorCount * 8, 256>>>(A);
+        e = cudaGetLastError();
+        ctx->launches++;
+    }
+    unsigned long long host[9] = {0};
+    if (e == cudaSuccess) e = cudaMemcpy(host, d_out, sizeof host, cudaMemcpyDeviceToHost);
+    cudaFree(d_out);
+    if (e != cudaSuccess) return fail(RTB200_ERR_CUDA, std::string("rtb200_filter_check: ") + cudaGetErrorString(e));
+    for (int k = 0; k < 9; k++) out[k] = host[k];
+    if (min_slack) { uint32_t bits = (uint32_t)host[8]; float f; std::memcpy(&f, &bits, 4); *min_slack = (double)f; }
     return RTB200_OK;
 }
 

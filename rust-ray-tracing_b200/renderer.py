@@ -103,6 +103,19 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_fp32_peak(self._ctx, int(iters), C.byref(tf), C.byref(ms)))
         return tf.value, ms.value
 
+    def filter_check(self, scene: Scene, n_rays: int, per_ray: int = 8, seed: int = 1, camera_point=None) -> dict:
+        """rtb200_filter_check: brute-forces n_rays * per_ray adversarial (ray, sphere) pairs of `scene` on the device —
+        the sweep's two conservative FP32 filters against the exact f64 discriminant, all in the arithmetic the render
+        kernels run.  false_negatives / slab_false_negatives must be 0."""
+        if self._scene is not scene:
+            self.upload_scene(scene)
+        out = (C.c_uint64 * 9)()
+        slack = C.c_double()
+        cam = (C.c_double * 3)(*camera_point) if camera_point is not None else None
+        _abi.check(_abi.lib.rtb200_filter_check(self._ctx, int(n_rays), int(per_ray), int(seed) & 0xFFFFFFFF, cam, out, C.byref(slack)))
+        return {"pairs": int(out[0]), "exact_positive": int(out[1]), "filter_candidates": int(out[2]), "false_negatives": int(out[3]),
+                "slab_candidates": [int(out[4]), int(out[5]), int(out[6])], "slab_false_negatives": int(out[7]), "min_slack": slack.value}
+
     def set_progress(self, callback=None, interval_ms: int = 100) -> None:
         """callback(items_claimed, items_total, elapsed_seconds) is called from render() every interval_ms while the
         trace kernel runs and once when it has finished (the reference's progress grid, src/renderer.rs:300-365, as a

@@ -5,7 +5,8 @@ The reference has no tests, fixtures or images for this path, cannot be built he
 randomness from the OS, so these are NOT outputs of the reference: they freeze the oracle, which is pinned
 by the hand-derived known-answer vectors in tests/test_oracle_kat.py and the Random123 Philox vectors.  What they buy:
   * the oracle cannot drift silently (compiler, flags, an edit to rt_oracle.hpp): tests/test_golden.py (CPU) re-runs it
-    against these files bit for bit, for both scalar types;
+    against these files bit for bit, in both modes: "f64" (reference-faithful) and "mix" (the GPU comparand: FP32 path
+    state, closest-hit sweep in f64 — what the CUDA kernels compute);
   * the CUDA path is checked on the GPU box against files that were written HERE, by a different build of the oracle
     on a different machine (tests/test_golden.py, -m gpu);
   * the three-sphere scene in the reference's TOML schema (three_spheres.toml) is what every host (Python,
@@ -43,11 +44,11 @@ def main():
         out = {"W": W, "H": H, "spp": spp, "depth": depth, "seed": seed, "cam18": np.asarray(cam.vectors(), dtype=np.float64)}
         for k, a in zip(("spheres", "mat_index", "kind", "hollow", "albedo", "param"), arrays):
             out[k] = np.asarray(a)
-        for tag, f32 in (("f32", True), ("f64", False)):
+        for tag, f32 in (("mix", True), ("f64", False)):   # mix = the GPU comparand (FP32 state, f64 hit routine), oracle_lib._mode
             s, rgb, seg = oracle.render(arrays, W, H, cam.vectors(), spp, depth, seed=seed, f32=f32, threads=1)
             out["sum_" + tag], out["rgb8_" + tag], out["segments_" + tag] = s, rgb, np.uint64(seg)
         np.savez_compressed(os.path.join(HERE, f"render_{name}.npz"), **out)
-        print(name, W, H, spp, "segments", int(out["segments_f32"]), int(out["segments_f64"]))
+        print(name, W, H, spp, "segments", int(out["segments_mix"]), int(out["segments_f64"]))
 
     # ray batch against the random-spheres scene: camera-like rays, rays from inside the scene, non-unit directions,
     # a few disabled lanes
@@ -66,11 +67,11 @@ def main():
     enabled = (rng.random(m) > 0.05).astype(np.int32)
     rays = np.concatenate([o, d], axis=1)
     out = {"spheres": spheres, "rays": rays, "enabled": enabled}
-    for tag, f32 in (("f32", True), ("f64", False)):
+    for tag, f32 in (("mix", True), ("f64", False)):   # mix = the GPU comparand (FP32 state, f64 hit routine), oracle_lib._mode
         idx, t = oracle.intersect(spheres, rays, enabled=enabled, f32=f32)
         out["idx_" + tag], out["t_" + tag] = idx, t
     np.savez_compressed(os.path.join(HERE, "intersect_random_spheres.npz"), **out)
-    print("intersect", m, "hits", int((out["idx_f32"] >= 0).sum()), "f32/f64 index disagreements", int((out["idx_f32"] != out["idx_f64"]).sum()))
+    print("intersect", m, "hits", int((out["idx_mix"] >= 0).sum()), "mix/f64 index disagreements", int((out["idx_mix"] != out["idx_f64"]).sum()))
 
     with open(os.path.join(HERE, "three_spheres.toml"), "w") as f:
         f.write("# BASELINE configs[0]: the three-sphere scene (diffuse / metal / glass + ground) in the reference's scene schema\n"

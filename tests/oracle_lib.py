@@ -27,6 +27,15 @@ _I = C.POINTER(C.c_int32)
 _U = C.POINTER(C.c_uint32)
 
 
+def _mode(f32) -> int:
+    """The oracle's scalar mode.  False: f64, reference-faithful.  True: the GPU comparand = MIXED (FP32 path state, the
+    closest-hit sweep in f64 on the f64 scene, the root rounded once to FP32 — what the CUDA kernels do).  "pure": FP32
+    throughout (what FP32 hit arithmetic would cost; no product path runs it)."""
+    if f32 == "pure":
+        return 2
+    return 1 if f32 else 0
+
+
 def _d(a):
     return a.ctypes.data_as(_D)
 
@@ -45,13 +54,13 @@ def philox(ctr, key):
 
 def cossin_2pi(v: float, f32: bool):
     cs, sn = C.c_double(), C.c_double()
-    _lib.oracle_cossin_2pi(C.c_double(v), int(f32), C.byref(cs), C.byref(sn))
+    _lib.oracle_cossin_2pi(C.c_double(v), _mode(f32), C.byref(cs), C.byref(sn))
     return cs.value, sn.value
 
 
 def unit_vector_from(u: float, v: float, f32: bool):
     out = (C.c_double * 3)()
-    _lib.oracle_unit_vector_from(C.c_double(u), C.c_double(v), int(f32), out)
+    _lib.oracle_unit_vector_from(C.c_double(u), C.c_double(v), _mode(f32), out)
     return np.array(out[:])
 
 
@@ -67,7 +76,7 @@ def camera_get_ray(width, height, cam18, col, row, rnd4, f32: bool):
     out = (C.c_double * 6)()
     cam = np.ascontiguousarray(cam18, dtype=np.float64)
     r = (C.c_uint32 * 4)(*rnd4)
-    _lib.oracle_camera_get_ray(int(width), int(height), _d(cam), int(col), int(row), r, int(f32), out)
+    _lib.oracle_camera_get_ray(int(width), int(height), _d(cam), int(col), int(row), r, _mode(f32), out)
     return np.array(out[:])
 
 
@@ -86,7 +95,7 @@ def intersect(spheres, rays, enabled=None, f32: bool = True):
     en = None
     if enabled is not None:
         en = np.ascontiguousarray(enabled, dtype=np.int32)
-    _lib.oracle_intersect(_d(sp), int(sp.shape[0]), _d(ry), _i(en) if en is not None else None, C.c_int64(m), int(f32), _i(idx), _d(t))
+    _lib.oracle_intersect(_d(sp), int(sp.shape[0]), _d(ry), _i(en) if en is not None else None, C.c_int64(m), _mode(f32), _i(idx), _d(t))
     return idx, t
 
 
@@ -96,7 +105,7 @@ def hit_and_scatter(sphere4, kind, hollow, albedo, param, ray6, rnd4, f32: bool)
     d3 = (C.c_double * 3)(*albedo)
     d6 = (C.c_double * 6)(*ray6)
     r = (C.c_uint32 * 4)(*rnd4)
-    _lib.oracle_hit_and_scatter(d4, int(kind), int(hollow), d3, C.c_double(param), d6, r, int(f32), out)
+    _lib.oracle_hit_and_scatter(d4, int(kind), int(hollow), d3, C.c_double(param), d6, r, _mode(f32), out)
     o = np.array(out[:])
     return {"hit": bool(o[0]), "t": o[1], "p": o[2:5], "n": o[5:8], "front": bool(o[8]), "attenuation": o[9:12],
             "origin": o[12:15], "direction": o[15:18]}
@@ -104,7 +113,7 @@ def hit_and_scatter(sphere4, kind, hollow, albedo, param, ray6, rnd4, f32: bool)
 
 def sky(d3, f32: bool):
     out = (C.c_double * 3)()
-    _lib.oracle_sky((C.c_double * 3)(*d3), int(f32), out)
+    _lib.oracle_sky((C.c_double * 3)(*d3), _mode(f32), out)
     return np.array(out[:])
 
 
@@ -113,11 +122,11 @@ _lib.oracle_reflectance.restype = C.c_double
 
 
 def quantise(c: float, f32: bool) -> int:
-    return int(_lib.oracle_quantise(C.c_double(c), int(f32)))
+    return int(_lib.oracle_quantise(C.c_double(c), _mode(f32)))
 
 
 def reflectance(cosine: float, ior: float, f32: bool) -> float:
-    return float(_lib.oracle_reflectance(C.c_double(cosine), C.c_double(ior), int(f32)))
+    return float(_lib.oracle_reflectance(C.c_double(cosine), C.c_double(ior), _mode(f32)))
 
 
 def render(scene_arrays, width, height, cam18, spp, depth, seed=1, sample_range=None, row_range=None, threads=None,
@@ -140,7 +149,7 @@ def render(scene_arrays, width, height, cam18, spp, depth, seed=1, sample_range=
     seg = C.c_uint64(0)
     _lib.oracle_render(_d(sp), _i(mi), int(sp.shape[0]), _i(kd), _i(hl), _d(al), _d(pr), int(kd.shape[0]), int(width), int(height),
                        _d(cam), int(s0), int(s1), int(spp), int(depth), C.c_uint32(seed & 0xFFFFFFFF), C.c_uint32((seed >> 32) & 0xFFFFFFFF),
-                       int(r0), int(r1), int(threads), int(f32), _d(out_sum),
+                       int(r0), int(r1), int(threads), _mode(f32), _d(out_sum),
                        out_rgb.ctypes.data_as(C.POINTER(C.c_uint8)) if want_rgb8 else None, C.byref(seg))
     return out_sum, out_rgb, int(seg.value)
 

@@ -1,9 +1,11 @@
-"""GPU parity tests: the CUDA path (through the C ABI) against oracle<float> on the same seeded inputs.
+"""GPU parity tests: the CUDA path (through the C ABI) against the oracle on the same seeded inputs.
 
-Tolerances (BASELINE.json north_star): intersection — hit/miss and object index exact, t within 1e-5 relative;
-deterministic-mode images — per-channel max abs difference <= 1e-4 before quantisation.  Because the kernels keep the
-reference's operation order and FMA placement, the comparison against oracle<float> is in fact bit-exact, and the
-tests assert that stronger property too (t bit-equal, RGB8 identical, segment counts identical)."""
+Tolerances (BASELINE.json north_star): intersection — hit/miss and object index exact, t within 1e-5 relative, against the
+reference's hit routine, which is f64: asserted against oracle<double> (`f32=False`) on every ray batch below;
+deterministic-mode images — per-channel max abs difference <= 1e-4 before quantisation, against the oracle's GPU comparand
+(`f32=True` = the MIXED mode of rt_oracle.hpp: FP32 path state, the closest-hit sweep in f64).  Because the kernels keep the
+reference's operation order and FMA placement, that comparison is in fact bit-exact, and the tests assert the stronger
+property too (t bit-equal, RGB8 identical, segment counts identical)."""
 import numpy as np
 import pytest
 
@@ -36,6 +38,12 @@ def _check_intersect(renderer, oracle, scene, o, d, enabled=None):
     rel = np.abs(t[hit].astype(np.float64) - rt[hit]) / np.abs(rt[hit])
     assert rel.max(initial=0.0) <= 1e-5
     assert np.array_equal(t[hit].astype(np.float64), rt[hit])   # bit-exact in practice
+    # the north_star's bar proper: against the reference-faithful f64 routine on the same (FP32-valued) rays
+    idx64, t64 = oracle.intersect(scene.arrays()[0], rays, enabled, f32=False)
+    assert np.array_equal(idx, idx64), f"{(idx != idx64).sum()} of {len(idx)} indices differ from the f64 routine"
+    rel64 = np.abs(t[hit].astype(np.float64) - t64[hit]) / np.abs(t64[hit])
+    assert rel64.max(initial=0.0) <= 1e-5, rel64.max()
+    assert np.array_equal(t[hit], t64[hit].astype(np.float32))  # the f64 root, rounded once
     return idx, t
 
 
@@ -566,3 +574,26 @@ def test_intersect_wild_scene(rtb, renderer, oracle):
     d = (rng.uniform(-20, 20, size=(20000, 3)) - o).astype(np.float32) * rng.uniform(0.01, 3.0, size=(20000, 1)).astype(np.float32)
     idx, _ = _check_intersect(renderer, oracle, scene, o, d)
     assert (idx >= 0).mean() > 0.5
+
+
+@pytest.mark.parametrize("scene_name,cam", [("random_spheres", (13.0, 2.0, 3.0)), ("ten_k_spheres", (13.0, 2.0, 3.0)), ("dielectric_heavy", (16.0, 2.0, 18.5)),
+                                            ("wild", (45.0, 12.0, 50.0)), ("tube", (0.3, 0.2, 2.0))])
+def test_filters_have_no_false_negatives_on_the_device(rtb, renderer, scene_name, cam):
+    """The parity of every sweep rests on its two FP32 filters never rejecting a pair the exact f64 test accepts.
+    oracle/filter_check.cpp checks that for the HOST build of rt_filter.h (IEEE 1/sqrt); the kernels run the DEVICE build
+    (approximate rsqrtf, __fmaf_rn).  rtb200_filter_check brute-forces >= 1e8 adversarial near-silhouette pairs per scene
+    family with the device arithmetic itself — make_filter / make_slab_ray / filter_value / slab_value against
+    exact_discriminant, the functions the render kernels inline — and must find no false negative."""
+    if scene_name == "wild":
+        scene = _wild_scene(rtb, 2000, 7)
+    elif scene_name == "tube":
+        scene = _tube_scene(rtb, 700)
+    else:
+        scene = getattr(rtb.scenes, scene_name)()
+    r = renderer.filter_check(scene, n_rays=13_000_000, per_ray=8, seed=11, camera_point=cam)
+    assert r["pairs"] == 104_000_000
+    assert r["false_negatives"] == 0 and r["slab_false_negatives"] == 0, r
+    assert r["exact_positive"] > 0.02 * r["pairs"], r          # the sample really contains hits ...
+    assert r["filter_candidates"] < 4 * r["exact_positive"], r  # ... and the filter is not vacuous on silhouette-aimed rays
+    assert r["min_slack"] > 0.3, r                            # worst observed error used well under the proven margin
+    print(scene_name, r)

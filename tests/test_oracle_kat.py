@@ -7,7 +7,7 @@ import math
 import numpy as np
 import pytest
 
-F = (False, True)   # f64 oracle, f32 oracle
+F = (False, True, "pure")   # the oracle's three modes: f64 (reference-faithful), mixed (the GPU comparand), pure FP32
 
 
 def test_philox_random123_kat(oracle):
