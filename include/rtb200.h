@@ -125,6 +125,8 @@ typedef struct rtb200_stats {
 } rtb200_stats;
 
 typedef struct rtb200_ctx rtb200_ctx;
+/* Progress callback of rtb200_set_progress / rtb200_multi_set_progress (see there). */
+typedef void (*rtb200_progress_fn)(void* user, uint64_t items_claimed, uint64_t items_total, double elapsed_seconds);
 
 /* ---- lifetime ------------------------------------------------------------------------------------------ */
 
@@ -231,6 +233,51 @@ int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, i
                                int32_t image_width, int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel,
                                void* rgb8_dev, void* stream);
 
+/* ---- one call, N GPUs (single process) --------------------------------------------------------------------------------
+ * Renderer::render is ONE synchronous call that owns all of its parallelism: it spawns its workers, feeds them tiles from
+ * a queue and joins them before it returns (src/renderer.rs:38-40, :272-296, :367-369; sole caller src/main.rs:62-64).
+ * rtb200_multi is that call over the GPUs of one box: one host thread queues the trace kernel of every shard on its own
+ * device and stream, then every device runs the fused reduce+resolve kernel for its slice of the pixels, reading the
+ * partial sums of all shards directly from peer memory over NVLink (cudaDeviceEnablePeerAccess; no NCCL, no staging copy)
+ * and writing its RGB8 slice into the first device's image, which is copied to the caller's host buffer.  Without peer
+ * access between some pair of devices the partial images are copied to the first device instead (cudaMemcpyPeerAsync) and
+ * resolved there.
+ *
+ * Sharding = a grid of row_groups x sample_groups shards (row_groups * sample_groups = number of shards): shard g belongs
+ * to row group g / sample_groups and sample group g % sample_groups; it traces the scanlines r with
+ * r % row_groups == its row group (interleaved scanlines: the balanced static analogue of the reference's tile queue,
+ * src/renderer.rs:254-266) and its contiguous share of the sample range.  row_groups = 1 is pure sample-range sharding
+ * (the default: perfectly balanced), row_groups = number of shards is pure row sharding, anything between is tile + sample
+ * (BASELINE configs[2]).  The Philox counter carries the image pixel and the global sample index, so the image does not
+ * depend on the sharding beyond float summation order. */
+typedef struct rtb200_multi rtb200_multi;
+
+/* One shard per entry of `devices` (n_devices in 1..RTB200_MAX_PEERS; devices == NULL: devices 0 .. n_devices-1).  A device
+ * may be named more than once (several shards share it: oversubscription, and how the multi-device path is exercised on a
+ * one-GPU box).  The first entry is the root: it holds the final image. */
+int rtb200_multi_create(const int32_t* devices, int32_t n_devices, rtb200_multi** out);
+void rtb200_multi_destroy(rtb200_multi* m);
+/* Number of shards; *peer_access (may be null) = 1 when every pair of distinct devices has direct peer access. */
+int rtb200_multi_info(rtb200_multi* m, int32_t* n_shards, int32_t* peer_access);
+/* rtb200_upload_scene / rtb200_set_hit_mode on every shard. */
+int rtb200_multi_upload_scene(rtb200_multi* m, const rtb200_scene* scene);
+int rtb200_multi_set_hit_mode(rtb200_multi* m, int32_t mode);
+/* Progress over all shards (items claimed / total summed over the devices); see rtb200_set_progress. */
+int rtb200_multi_set_progress(rtb200_multi* m, rtb200_progress_fn fn, void* user, int32_t interval_ms);
+
+/* Renderer::render over all shards: the whole job named by `params` (its sample range and rows; row_stride must be 0 or 1
+ * and row_begin 0 when row_groups > 1), host buffers out as for rtb200_render.  linear_rgba_out, when not null, receives
+ * the per-pixel SUM over all shards (r, g, b, sample count) as the reduce kernel formed it.  stats: counters summed over
+ * the shards, trace_ms / resolve_ms = the slowest shard's. */
+int rtb200_multi_render(rtb200_multi* m, const rtb200_camera* camera, const rtb200_params* params, int32_t row_groups,
+                        uint8_t* rgb8_out, float* linear_rgba_out, rtb200_stats* stats);
+
+/* rtb200_resolve_grid_device that also stores the summed float4 image for its pixel range into sum_dev (a WHOLE-image float4
+ * buffer, local or a peer's; null = not wanted): how a caller of the multi-GPU path gets the linear image before quantisation. */
+int rtb200_resolve_grid_sum_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups,
+                                   int32_t image_width, int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel,
+                                   void* rgb8_dev, void* sum_dev, void* stream);
+
 /* Device counters of the last trace on this context (valid after the stream has been synchronised). */
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
 
@@ -239,7 +286,6 @@ int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments);
  * calls fn(user, items_claimed, items_total, elapsed_seconds) every interval_ms milliseconds from the calling thread,
  * and once more with items_claimed == items_total when the kernel has finished.  A work item is one pixel's share of
  * the sample range (what a path slot claims from the device work queue).  fn == NULL switches it off. */
-typedef void (*rtb200_progress_fn)(void* user, uint64_t items_claimed, uint64_t items_total, double elapsed_seconds);
 int rtb200_set_progress(rtb200_ctx* ctx, rtb200_progress_fn fn, void* user, int32_t interval_ms);
 
 /* Selects the hit mode (RTB200_HIT_*) of every later rtb200_render / rtb200_trace_device / rtb200_intersect_batch on

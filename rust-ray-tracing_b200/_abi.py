@@ -72,6 +72,14 @@ SYMBOLS = {
     "rtb200_ipc_close": (C.c_int, [_P, _P]),
     "rtb200_resolve_peers_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_resolve_grid_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
+    "rtb200_resolve_grid_sum_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P, _P]),
+    "rtb200_multi_create": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(_P)]),
+    "rtb200_multi_destroy": (None, [_P]),
+    "rtb200_multi_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "rtb200_multi_upload_scene": (C.c_int, [_P, C.POINTER(Scene)]),
+    "rtb200_multi_set_hit_mode": (C.c_int, [_P, C.c_int32]),
+    "rtb200_multi_set_progress": (C.c_int, [_P, C.c_void_p, C.c_void_p, C.c_int32]),
+    "rtb200_multi_render": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), C.c_int32, _P, _P, C.POINTER(Stats)]),
     "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtb200_launch_count": (C.c_int64, [_P]),
     "rtb200_set_hit_mode": (C.c_int32, [_P, C.c_int32]),

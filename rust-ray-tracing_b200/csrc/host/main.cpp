@@ -27,6 +27,10 @@ void usage() {
         "  --depth N               max bounces                                 [50]\n"
         "  --seed N                Philox key of the sample stream             [1]\n"
         "  --device N              CUDA device                                 [0]\n"
+        "  --gpus N                render on devices 0..N-1 in ONE call (rtb200_multi_render: traces sharded over the GPUs,\n"
+        "                          partial framebuffers summed over NVLink peer memory by the resolve kernel)   [1]\n"
+        "  --devices A,B,...       the same on the named devices (a device may repeat)\n"
+        "  --sharding MODE         samples (default) | rows | RxS (R interleaved-scanline groups x S sample groups)\n"
         "  --focal-length F --view-angle DEG --defocus-angle DEG               [10, 30, 0]\n"
         "  --center X,Y,Z --look-at X,Y,Z --up X,Y,Z                           [16,2,18.5  0,0,0  0,1,0]\n"
         "  --camera-from-scene     use the scene file's [camera] table (Camera::from_toml keys)\n"
@@ -60,6 +64,8 @@ int main(int argc, char** argv) {
     bool dump_toml = false, dump_scene = false, dump_camera = false, stats_json = false, quiet = false, camera_from_scene = false;
     bool both_roots = false, progress = false;
     bool have_scene_arg = false;
+    std::vector<int32_t> devices;                                       // --gpus / --devices: the shards of rtb200_multi
+    std::string sharding = "samples";
     for (int i = 1; i < argc; i++) {
         std::string a = argv[i];
         auto need = [&](const char* name) -> const char* {
@@ -74,6 +80,14 @@ int main(int argc, char** argv) {
         else if (a == "--depth") depth = std::atoi(need("--depth"));
         else if (a == "--seed") seed = std::strtoull(need("--seed"), nullptr, 10);
         else if (a == "--device") device = std::atoi(need("--device"));
+        else if (a == "--gpus") { const int n = std::atoi(need("--gpus")); devices.clear(); for (int g = 0; g < n; g++) devices.push_back(g); }
+        else if (a == "--devices") {
+            devices.clear();
+            std::stringstream ss(need("--devices"));
+            std::string tok;
+            while (std::getline(ss, tok, ',')) if (!tok.empty()) devices.push_back(std::atoi(tok.c_str()));
+        }
+        else if (a == "--sharding") sharding = need("--sharding");
         else if (a == "--focal-length") cam.focal_length = std::atof(need("--focal-length"));
         else if (a == "--view-angle") cam.view_angle = std::atof(need("--view-angle"));
         else if (a == "--defocus-angle") cam.defocus_angle = std::atof(need("--defocus-angle"));
@@ -134,13 +148,32 @@ int main(int argc, char** argv) {
     }
 
     rtb200_ctx* ctx = nullptr;
+    rtb200_multi* multi = nullptr;
     auto die = [&](const char* what) {
         std::fprintf(stderr, "rtb200_cli: %s: %s\n", what, rtb200_last_error());
         if (ctx) rtb200_destroy(ctx);
+        if (multi) rtb200_multi_destroy(multi);
         return 1;
     };
-    if (rtb200_create(device, &ctx) != RTB200_OK) return die("rtb200_create");           // TileRenderer::new, src/main.rs:62
-    if (both_roots && rtb200_set_hit_mode(ctx, RTB200_HIT_BOTH_ROOTS) != RTB200_OK) return die("rtb200_set_hit_mode");
+    int row_groups = 1;
+    if (!devices.empty()) {   // several GPUs behind the one render call (the reference's render owns its worker threads the same way)
+        const int n = (int)devices.size();
+        if (sharding == "samples") row_groups = 1;
+        else if (sharding == "rows") row_groups = n;
+        else {
+            int r = 0, sgr = 0;
+            if (std::sscanf(sharding.c_str(), "%dx%d", &r, &sgr) != 2 || r < 1 || sgr < 1 || r * sgr != n) {
+                std::fprintf(stderr, "rtb200_cli: --sharding wants samples, rows or RxS with R*S = %d shards\n", n);
+                return 2;
+            }
+            row_groups = r;
+        }
+        if (rtb200_multi_create(devices.data(), n, &multi) != RTB200_OK) return die("rtb200_multi_create");
+        if (both_roots && rtb200_multi_set_hit_mode(multi, RTB200_HIT_BOTH_ROOTS) != RTB200_OK) return die("rtb200_multi_set_hit_mode");
+    } else {
+        if (rtb200_create(device, &ctx) != RTB200_OK) return die("rtb200_create");       // TileRenderer::new, src/main.rs:62
+        if (both_roots && rtb200_set_hit_mode(ctx, RTB200_HIT_BOTH_ROOTS) != RTB200_OK) return die("rtb200_set_hit_mode");
+    }
     if (progress) {   // src/renderer.rs:300-365 draws a tile grid; one line is enough for a render that takes milliseconds to seconds
         auto draw = [](void*, uint64_t done, uint64_t total, double secs) {
             const double frac = total ? (double)done / (double)total : 1.0;
@@ -153,10 +186,11 @@ int main(int argc, char** argv) {
             if (done == total) std::fputc('\n', stderr);
             std::fflush(stderr);
         };
-        if (rtb200_set_progress(ctx, draw, nullptr, 100) != RTB200_OK) return die("rtb200_set_progress");
+        if ((multi ? rtb200_multi_set_progress(multi, draw, nullptr, 100) : rtb200_set_progress(ctx, draw, nullptr, 100)) != RTB200_OK)
+            return die("rtb200_set_progress");
     }
     rtb200_scene abi = scene.abi();
-    if (rtb200_upload_scene(ctx, &abi) != RTB200_OK) return die("rtb200_upload_scene");  // Scene::from_list, src/main.rs:43
+    if ((multi ? rtb200_multi_upload_scene(multi, &abi) : rtb200_upload_scene(ctx, &abi)) != RTB200_OK) return die("rtb200_upload_scene");  // Scene::from_list, src/main.rs:43
     rtb200_params params;
     std::memset(&params, 0, sizeof params);
     params.max_bounces = depth; params.samples_per_pixel = spp; params.seed = seed;
@@ -165,7 +199,9 @@ int main(int argc, char** argv) {
     void* pinned = nullptr;
     if (rtb200_host_alloc(n_bytes, &pinned) != RTB200_OK) return die("rtb200_host_alloc");
     rtb200_stats st;
-    if (rtb200_render(ctx, &camera, &params, static_cast<uint8_t*>(pinned), nullptr, &st) != RTB200_OK) {   // renderer.render(50, 100, ..), src/main.rs:64
+    const int render_rc = multi ? rtb200_multi_render(multi, &camera, &params, row_groups, static_cast<uint8_t*>(pinned), nullptr, &st)
+                                : rtb200_render(ctx, &camera, &params, static_cast<uint8_t*>(pinned), nullptr, &st);
+    if (render_rc != RTB200_OK) {   // renderer.render(50, 100, ..), src/main.rs:64
         rtb200_host_free(pinned);
         return die("rtb200_render");
     }
@@ -185,10 +221,11 @@ int main(int argc, char** argv) {
     }
     if (stats_json)
         std::printf("{\"seconds\": %.6f, \"pixels\": %llu, \"paths\": %llu, \"segments\": %llu, \"sphere_tests\": %llu, \"trace_ms\": %.4f, "
-                    "\"resolve_ms\": %.4f, \"d2h_ms\": %.4f, \"mpaths_per_s\": %.3f}\n",
+                    "\"resolve_ms\": %.4f, \"d2h_ms\": %.4f, \"mpaths_per_s\": %.3f, \"shards\": %d, \"row_groups\": %d}\n",
                     st.seconds, (unsigned long long)st.pixels_rendered, (unsigned long long)st.paths, (unsigned long long)st.segments,
                     (unsigned long long)st.sphere_tests, st.trace_ms, st.resolve_ms, st.d2h_ms,
-                    st.trace_ms > 0 ? (double)st.paths / (st.trace_ms * 1e-3) * 1e-6 : 0.0);
-    rtb200_destroy(ctx);
+                    st.trace_ms > 0 ? (double)st.paths / (st.trace_ms * 1e-3) * 1e-6 : 0.0, multi ? (int)devices.size() : 1, row_groups);
+    if (ctx) rtb200_destroy(ctx);
+    if (multi) rtb200_multi_destroy(multi);
     return rc;
 }

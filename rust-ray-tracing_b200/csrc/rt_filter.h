@@ -83,6 +83,16 @@ RTB_HD float filter_value(const FilterRay& f, float cx, float cy, float cz, floa
     return RTB_FMA(h, h, -w);
 }
 
+// The same, also handing back h = (c - o).D, the FP32 projection of the centre on the ray (stage 2 of the two-stage sweep
+// uses its sign to drop spheres behind the origin).  |h - (c - o).d/|d|| <= 8u(|o| + |c| + r): direction normalisation u|OC|,
+// three roundings each in -(o.D) and in the chain, f32 centre against the f64 centre u|c|.
+RTB_HD float filter_value_h(const FilterRay& f, float cx, float cy, float cz, float k, float& h) {
+    h = RTB_FMA(cx, f.hx, RTB_FMA(cy, f.hy, RTB_FMA(cz, f.hz, f.nod)));
+    float g = RTB_FMA(cx, f.gx, RTB_FMA(cy, f.gy, RTB_FMA(cz, f.gz, f.oo)));
+    float w = RTB_ADD(g, k);
+    return RTB_FMA(h, h, -w);
+}
+
 // Per-sphere half, evaluated in f64 on the host from the DEVICE values (float centre, float r^2):
 // k = |c|^2 - r^2 - 192u*(|c| + r)^2, rounded to float and stepped one ulp towards -inf.
 inline float filter_sphere_k(float cx, float cy, float cz, float r2) {

@@ -40,11 +40,20 @@ __device__ __forceinline__ void stage_spheres(float4* s_sph, const float4* __res
 // One ray as the exact candidate test needs it (origin, direction as stored: never normalised, src/ray.rs:13-18).
 // both_roots: warp-uniform hit mode (false = the reference's packed path: near root only; true = the scalar
 // Sphere::hit rule, src/objects.rs:227-234: the far root when the near one is out of range).
-struct ExactRay { float ox, oy, oz, dx, dy, dz; bool both_roots; };
+// inv_a = 1 / (d.d) in f64 (src/objects.rs:253-254), evaluated ONCE per ray and sweep (the division is the one expensive
+// f64 operation of the exact test) and carried with the ray: in registers, or parked in the two shared-memory words that
+// hold the sweep's result between trips.
+struct ExactRay { float ox, oy, oz, dx, dy, dz; double inv_a; bool both_roots; };
 
+__device__ __forceinline__ double exact_inv_a(f3 d) {
+    const double dx = (double)d.x, dy = (double)d.y, dz = (double)d.z;
+    const double a = __fma_rn(dz, dz, __fma_rn(dy, dy, __dmul_rn(dx, dx)));                         // src/objects.rs:253
+    return __drcp_rn(a);                                                                            // :254 (1.0 / a, correctly rounded)
+}
 __device__ __forceinline__ ExactRay make_exact_ray(f3 o, f3 d, bool both_roots) {
     ExactRay r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.both_roots = both_roots;
+    r.inv_a = exact_inv_a(d);
     return r;
 }
 // The ray's half of the candidate filter; a = d.d as the sweep computes it (src/objects.rs:253).
@@ -67,7 +76,7 @@ __device__ __forceinline__ ExactRay64 promote_ray(const ExactRay& r) {
     e.ox = (double)r.ox; e.oy = (double)r.oy; e.oz = (double)r.oz;
     e.dx = (double)r.dx; e.dy = (double)r.dy; e.dz = (double)r.dz;
     e.a = __fma_rn(e.dz, e.dz, __fma_rn(e.dy, e.dy, __dmul_rn(e.dx, e.dx)));                        // src/objects.rs:253
-    e.inv_a = __ddiv_rn(1.0, e.a);                                                                  // :254
+    e.inv_a = r.inv_a;                                                                              // :254, hoisted (exact_inv_a)
     return e;
 }
 
@@ -79,9 +88,15 @@ __device__ __forceinline__ double exact_discriminant(const ExactRay64& r, double
     const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), s.w);     // :256
     return __fma_rn(hb, hb, -__dmul_rn(r.a, cc));                                                     // :257
 }
+//
+// Near-root mode, half_b >= 0 (the sphere's centre is not ahead of the origin): root1 = (-half_b - sqrt(disc)) * inv_a is
+// <= 0 < 0.001 whatever disc is, so the lane is invalid in the reference too (:272-277) and the rest is skipped — exactly.
 __device__ __forceinline__ void test_candidate(const ExactRay64& r, bool both_roots, double4 s, int index, double& best_t, int& best_i) {
-    double hb;
-    const double disc = exact_discriminant(r, s, hb);
+    const double ocx = __dsub_rn(r.ox, s.x), ocy = __dsub_rn(r.oy, s.y), ocz = __dsub_rn(r.oz, s.z);   // :252
+    const double hb = __fma_rn(ocz, r.dz, __fma_rn(ocy, r.dy, __dmul_rn(ocx, r.dx)));                  // :255
+    if (!both_roots && !(hb < 0.0)) return;
+    const double cc = __dsub_rn(__fma_rn(ocz, ocz, __fma_rn(ocy, ocy, __dmul_rn(ocx, ocx))), s.w);     // :256
+    const double disc = __fma_rn(hb, hb, -__dmul_rn(r.a, cc));                                        // :257
     if (disc >= 0.0) {                                                                             // :259
         const double T_MIN_D = 0.001, INF_D = __longlong_as_double(0x7ff0000000000000LL);          // 0.001..f64::INFINITY (src/ray_tracing.rs:400)
         const double sq = __dsqrt_rn(disc);                                                        // :263
@@ -351,16 +366,23 @@ __device__ __forceinline__ bool walk_next(const uint32_t* masks_r, int stride, u
 }
 
 __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
-                                          const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, FilterRay f, ExactRay ray32,
-                                          Best best) {
+                                          const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, float h_bound, FilterRay f,
+                                          ExactRay ray32, Best best) {
     if (todo == 0u) return best;
     const ExactRay64 ray = promote_ray(ray32);
+    // Near-root mode: a sphere whose centre lies behind the origin along the ray (half_b > 0) cannot give a valid root
+    // (test_candidate).  The filter's own h = (c - o).D is that projection in FP32, off by at most 8u(|o| + |c| + r)
+    // (rt_filter.h), so h < -16u(|o|_1 + max(|c| + r)) proves half_b > 0 and the f64 test is skipped: for a bounce ray
+    // in the middle of the scene that is half of the stage-2 survivors.
+    const float h_min = ray32.both_roots ? -RTB_INF : -__fmul_rn(9.5367431640625e-07f, __fadd_rn(__fadd_rn(fabsf(ray32.ox), fabsf(ray32.oy)), __fadd_rn(fabsf(ray32.oz), h_bound)));
     uint32_t cand = 0;
     int last = 0, idx = 0;                                 // last = index of the current block's sphere 31
     while (walk_next(masks_r, stride, todo, cand, last, first_sphere, idx)) {
         const float4 fs = __ldg(&g_filter[idx]);
-        const float q = filter_value(f, fs.x, fs.y, fs.z, fs.w);                                   // stage 2 (FP32, conservative)
-        if (!(__float_as_uint(q) >> 31)) test_candidate(ray, ray32.both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);   // stage 3 (f64, exact)
+        float h;
+        const float q = filter_value_h(f, fs.x, fs.y, fs.z, fs.w, h);                              // stage 2 (FP32, conservative)
+        if (!(__float_as_uint(q) >> 31) && !(h < h_min))
+            test_candidate(ray, ray32.both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);   // stage 3 (f64, exact)
     }
     return best;
 }
@@ -408,7 +430,7 @@ struct SmemSlab {
 
 template <int RAYS, class S1, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const float4* __restrict__ g_filter,
-                                                const double4* __restrict__ g_exact, int count, uint32_t* masks, int stride,
+                                                const double4* __restrict__ g_exact, float h_bound, int count, uint32_t* masks, int stride,
                                                 const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
     for (int cb = 0; cb < n_blocks; cb += 8) {
@@ -434,7 +456,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -459,7 +481,7 @@ constexpr int STREAM_CHUNK_F4 = 8 * SWEEP_BLOCK * 3 / 4;     // float4 per chunk
 
 template <int RAYS, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float4* __restrict__ g_s1, unsigned lane, const RaySrc& rays,
-                                                       const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, int n_padded,
+                                                       const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, float h_bound, int n_padded,
                                                        uint32_t* masks, int stride, const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS],
                                                        double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = n_padded / SWEEP_BLOCK;              // the device arrays are padded to whole blocks
@@ -499,7 +521,7 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays.load(r), bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -600,6 +622,7 @@ struct TraceParams {
     const float4* spheres;        // FP32 {cx,cy,cz,r*r}: shading (finalize_hit)
     const float4* filter;         // candidate filter: {cx,cy,cz,k} (rt_filter.h): the one-stage sweeps, stage 2 of the two-stage sweep
     const double4* exact;         // f64 {cx,cy,cz,r*r}: the exact candidate test (test_candidate)
+    float h_bound;                // max over the scene of |c| + r, rounded up (refine_chunk's behind-the-origin rejection)
     const float4* mat;            // per sphere {albedo rgb, param}
     const int* mat_kind;          // per sphere kind | hollow<<8
     int n_spheres;
@@ -992,7 +1015,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
             bt[r] = RTB_INF_D;
             best_i[r] = -1;
         }
-        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, P.filter, P.exact, P.n_spheres, masks, THREADS, slab, flt, bt, best_i);
+        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, P.filter, P.exact, P.h_bound, P.n_spheres, masks, THREADS, slab, flt, bt, best_i);
 #pragma unroll
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
@@ -1051,7 +1074,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
             bt[r] = RTB_INF_D;
             best_i[r] = -1;
         }
-        sweep_two_stage_stream<RAYS>(wbuf, PV.s1, lane, RegisterRays{ray}, P.filter, P.exact, PV.n_padded, masks, THREADS, slab, flt, bt, best_i);
+        sweep_two_stage_stream<RAYS>(wbuf, PV.s1, lane, RegisterRays{ray}, P.filter, P.exact, P.h_bound, PV.n_padded, masks, THREADS, slab, flt, bt, best_i);
 #pragma unroll
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
@@ -1077,6 +1100,7 @@ struct SmemRays {
         e.ox = __uint_as_float(st[(0 * RAYS + r) * THREADS]); e.oy = __uint_as_float(st[(1 * RAYS + r) * THREADS]);
         e.oz = __uint_as_float(st[(2 * RAYS + r) * THREADS]); e.dx = __uint_as_float(st[(3 * RAYS + r) * THREADS]);
         e.dy = __uint_as_float(st[(4 * RAYS + r) * THREADS]); e.dz = __uint_as_float(st[(5 * RAYS + r) * THREADS]);
+        e.inv_a = __hiloint2double((int)st[(16 * RAYS + r) * THREADS], (int)st[(15 * RAYS + r) * THREADS]);   // parked by the kernel before the sweep
         return e;
     }
 };
@@ -1145,6 +1169,10 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             flt[r] = make_filter(mk3(F(0, r), F(1, r), F(2, r)), mk3(F(3, r), F(4, r), F(5, r)));
+            // 1 / (d.d) in f64 for the exact test, once per ray and sweep: parked in the slot's two result words (15, 16), which
+            // are free until the sweep's result overwrites them below
+            const double inv_a = exact_inv_a(mk3(F(3, r), F(4, r), F(5, r)));
+            W(15, r) = (uint32_t)__double2loint(inv_a); W(16, r) = (uint32_t)__double2hiint(inv_a);
             best_t[r] = RTB_INF_D;
             best_i[r] = -1;
         }
@@ -1155,9 +1183,9 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             if constexpr (PV_T::s1_smem)
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
             else
-                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.n_spheres, list, THREADS, slab,
+                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab,
                                       flt, best_t, best_i);
         } else {
             sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.exact, P.n_spheres, list, THREADS,
@@ -1210,11 +1238,12 @@ __global__ void __launch_bounds__(256) k_resolve(const float4* __restrict__ accu
 
 // ---- K3p: fused peer reduce + resolve.  Each thread owns 4 consecutive pixels: it loads their float4 partial sums from
 // every rank's accumulation image (its own HBM and, over NVLink, the peers'), adds them in rank order, and stores 12
-// bytes of RGB8 (possibly into a peer's image).  All loads of a thread are issued before the first add.
+// bytes of RGB8 (possibly into a peer's image) and, on request, the summed float4 (sum_out, null = not wanted).  All loads
+// of a thread are issued before the first add.
 struct PeerPtrs { const float4* p[16]; };
 
 __global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ PeerPtrs peers, int n_peers, int row_groups, int width, long long pixel_begin,
-                                                       long long pixel_end, float spp, uint8_t* __restrict__ rgb8) {
+                                                       long long pixel_end, float spp, uint8_t* __restrict__ rgb8, float4* __restrict__ sum_out) {
     // peers.p[g * n_peers + k]: partial image of sample group k of row group g; image row r belongs to row group
     // r % row_groups (interleaved scanlines).  row_groups == 1: every pixel sums peers.p[0 .. n_peers).
     long long p0 = pixel_begin + ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -1242,6 +1271,9 @@ __global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ P
                     acc[k].z = __fadd_rn(acc[k].z, v[gg][k].z); acc[k].w = __fadd_rn(acc[k].w, v[gg][k].w);
                 }
             }
+    }
+    if (sum_out) {                                           // the summed linear image (local or a peer's), for callers that want it
+        for (int k = 0; k < n; k++) sum_out[p0 + k] = acc[k];
     }
     uint32_t b[12];
 #pragma unroll

@@ -71,6 +71,7 @@ struct rtb200_ctx {
     double4* d_exact = nullptr;                        // {cx, cy, cz, r*r} in f64, list order, padded: the exact candidate test of every sweep
     float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
     int n_padded = 32;
+    float h_bound = 0.0f;                              // max |c| + r over the scene, rounded up (TraceParams::h_bound)
     int largest_sphere = 0;                            // index of the sphere with the largest radius (rtb200_filter_check)
     int n_spheres = 0;
     // counters: [0] paths [1] segments [2] work counter
@@ -156,7 +157,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const int n_samples = p->sample_end - p->sample_begin;
     rtb::TraceParams P;
     P.cam = device_camera(*cam);
-    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.exact = ctx->d_exact; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
+    P.spheres = ctx->d_spheres; P.filter = ctx->d_filter; P.exact = ctx->d_exact; P.h_bound = ctx->h_bound; P.mat = ctx->d_mat; P.mat_kind = ctx->d_mat_kind;
     P.n_spheres = ctx->n_spheres;
     P.max_bounces = p->max_bounces;
     P.seed_lo = (uint32_t)(p->seed & 0xffffffffu); P.seed_hi = (uint32_t)(p->seed >> 32);
@@ -545,6 +546,11 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
     ctx->d_mat_kind = reinterpret_cast<int*>(base + off_kind);
     ctx->n_padded = (int)cnt;
     ctx->largest_sphere = 0;
+    {
+        double hb = 0.0;
+        for (int i = 0; i < n; i++) hb = std::max(hb, std::sqrt((double)sph[i].x * sph[i].x + (double)sph[i].y * sph[i].y + (double)sph[i].z * sph[i].z) + std::fabs(scene->spheres[i].radius));
+        ctx->h_bound = std::nextafterf((float)(hb * (1.0 + 1e-6)), INFINITY);
+    }
     for (int i = 1; i < n; i++) if (sph[i].w > sph[ctx->largest_sphere].w) ctx->largest_sphere = i;
     ctx->n_spheres = n;
     ctx->h_filter.assign(flt.begin(), flt.begin() + n);
@@ -706,7 +712,10 @@ int rtb200_render(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_par
         CU_TRY(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3])); stats->d2h_ms = ms;
         stats->paths = cnt[0]; stats->segments = cnt[1];
         stats->sphere_tests = cnt[1] * (unsigned long long)ctx->n_spheres;
-        stats->pixels_rendered = (uint64_t)(params->row_end - params->row_begin) * camera->image_width;   // RenderStat::new, src/renderer.rs:385
+        {   // RenderStat::new, src/renderer.rs:385: the pixels this call traced (every row_stride-th row of the range)
+            const int rs = params->row_stride > 1 ? params->row_stride : 1;
+            stats->pixels_rendered = (uint64_t)((params->row_end - params->row_begin + rs - 1) / rs) * camera->image_width;
+        }
         stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         stats->pixels_per_second = stats->seconds > 0 ? (double)stats->pixels_rendered / stats->seconds : 0.0;
     }
@@ -756,8 +765,8 @@ int rtb200_ipc_close(rtb200_ctx* ctx, void* dev) {
     return RTB200_OK;
 }
 
-int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups, int32_t image_width,
-                               int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+int rtb200_resolve_grid_sum_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups, int32_t image_width,
+                                   int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* sum_dev, void* stream) {
     if (!ctx || !accum_ptrs || !rgb8_dev) return fail(RTB200_ERR_INVALID, "null argument");
     if (row_groups < 1 || sample_groups < 1 || (int64_t)row_groups * sample_groups > RTB200_MAX_PEERS)
         return fail(RTB200_ERR_INVALID, "row_groups x sample_groups must be 1.." + std::to_string(RTB200_MAX_PEERS));
@@ -775,10 +784,17 @@ int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, i
     const long long quads = (pixel_end - pixel_begin + 3) / 4;
     const int blocks = (int)((quads + 255) / 256);
     rtb::k_resolve_peers<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(pp, sample_groups, row_groups, image_width, pixel_begin, pixel_end,
-                                                                               (float)samples_per_pixel, static_cast<uint8_t*>(rgb8_dev));
+                                                                               (float)samples_per_pixel, static_cast<uint8_t*>(rgb8_dev),
+                                                                               static_cast<float4*>(sum_dev));
     CU_TRY(cudaGetLastError());
     ctx->launches++;
     return RTB200_OK;
+}
+
+int rtb200_resolve_grid_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups, int32_t image_width,
+                               int64_t pixel_begin, int64_t pixel_end, int32_t samples_per_pixel, void* rgb8_dev, void* stream) {
+    return rtb200_resolve_grid_sum_device(ctx, accum_ptrs, row_groups, sample_groups, image_width, pixel_begin, pixel_end, samples_per_pixel, rgb8_dev,
+                                          nullptr, stream);
 }
 
 int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t n_peers, int64_t pixel_begin, int64_t pixel_end,
@@ -874,6 +890,294 @@ int rtb200_fp32_peak(rtb200_ctx* ctx, int32_t iters, double* tflops, double* ms_
     double flop = 2.0 * 8.0 * 16.0 * (double)iters * 1024.0 * (double)grid;
     if (tflops) *tflops = flop / ((double)best * 1e-3) * 1e-12;
     if (ms_out) *ms_out = best;
+    return RTB200_OK;
+}
+
+}  // extern "C"
+
+
+// ---- one call, N GPUs (single process): rtb200_multi -------------------------------------------------------------------------
+// Renderer::render is one synchronous call that owns its parallelism (src/renderer.rs:38-40, :272-296, :367-369).  Here one host
+// thread queues every shard's trace kernel on its own device and stream; cross-device events order the fused reduce+resolve
+// kernels (k_resolve_peers, one pixel slice per shard, peer loads over NVLink) behind ALL traces; the root's stream waits for all
+// slices and copies the image out.  No host synchronisation between the first launch and the final copy.
+struct rtb200_multi {
+    int n = 0;
+    std::vector<rtb200_ctx*> ctx;
+    std::vector<int> device;
+    std::vector<cudaStream_t> stream;
+    std::vector<cudaEvent_t> ev_start, ev_traced, ev_res0, ev_resolved;
+    std::vector<float4*> accum;                        // per shard: W*H float4 on its device
+    std::vector<float4*> staging;                      // no-peer-access fallback: the shards' images copied to the root device
+    size_t pixels = 0, staging_pixels = 0;
+    uint8_t* root_rgb8 = nullptr; size_t rgb8_bytes = 0;
+    float4* root_sum = nullptr; size_t sum_pixels = 0;
+    bool peer_ok = true;
+    rtb200_progress_fn progress_cb = nullptr; void* progress_user = nullptr; int progress_interval_ms = 100;
+};
+
+namespace {
+
+void multi_noop_progress(void*, uint64_t, uint64_t, double) {}
+
+int multi_ensure_buffers(rtb200_multi* m, size_t n_pix, bool want_sum) {
+    if (m->pixels < n_pix) {
+        for (int g = 0; g < m->n; g++) {
+            CU_TRY(cudaSetDevice(m->device[g]));
+            if (m->accum[g]) cudaFree(m->accum[g]);
+            m->accum[g] = nullptr;
+        }
+        m->pixels = 0;
+        for (int g = 0; g < m->n; g++) {
+            CU_TRY(cudaSetDevice(m->device[g]));
+            CU_TRY(cudaMalloc(&m->accum[g], n_pix * sizeof(float4)));
+            CU_TRY(cudaMemset(m->accum[g], 0, n_pix * sizeof(float4)));
+        }
+        m->pixels = n_pix;
+    }
+    CU_TRY(cudaSetDevice(m->device[0]));
+    if (m->rgb8_bytes < n_pix * 3 + 16) {
+        if (m->root_rgb8) cudaFree(m->root_rgb8);
+        m->root_rgb8 = nullptr; m->rgb8_bytes = 0;
+        CU_TRY(cudaMalloc(&m->root_rgb8, n_pix * 3 + 16));
+        m->rgb8_bytes = n_pix * 3 + 16;
+    }
+    if (want_sum && m->sum_pixels < n_pix) {
+        if (m->root_sum) cudaFree(m->root_sum);
+        m->root_sum = nullptr; m->sum_pixels = 0;
+        CU_TRY(cudaMalloc(&m->root_sum, n_pix * sizeof(float4)));
+        m->sum_pixels = n_pix;
+    }
+    if (!m->peer_ok && m->staging_pixels < n_pix) {
+        for (int g = 1; g < m->n; g++) {
+            if (m->staging[g]) cudaFree(m->staging[g]);
+            m->staging[g] = nullptr;
+            CU_TRY(cudaMalloc(&m->staging[g], n_pix * sizeof(float4)));
+        }
+        m->staging_pixels = n_pix;
+    }
+    return RTB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtb200_multi_create(const int32_t* devices, int32_t n_devices, rtb200_multi** out) {
+    if (!out) return fail(RTB200_ERR_INVALID, "out is null");
+    *out = nullptr;
+    if (n_devices < 1 || n_devices > RTB200_MAX_PEERS) return fail(RTB200_ERR_INVALID, "n_devices must be 1.." + std::to_string(RTB200_MAX_PEERS));
+    rtb200_multi* m = new rtb200_multi();
+    m->n = n_devices;
+    m->ctx.assign(n_devices, nullptr); m->device.assign(n_devices, 0); m->stream.assign(n_devices, nullptr);
+    m->ev_start.assign(n_devices, nullptr); m->ev_traced.assign(n_devices, nullptr); m->ev_res0.assign(n_devices, nullptr);
+    m->ev_resolved.assign(n_devices, nullptr); m->accum.assign(n_devices, nullptr); m->staging.assign(n_devices, nullptr);
+    for (int g = 0; g < n_devices; g++) {
+        m->device[g] = devices ? devices[g] : g;
+        int rc = rtb200_create(m->device[g], &m->ctx[g]);
+        if (rc) { std::string keep = g_last_error; rtb200_multi_destroy(m); return fail(rc, "shard " + std::to_string(g) + ": " + keep); }
+        cudaError_t e = cudaStreamCreateWithFlags(&m->stream[g], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&m->ev_start[g]);
+        if (e == cudaSuccess) e = cudaEventCreate(&m->ev_traced[g]);
+        if (e == cudaSuccess) e = cudaEventCreate(&m->ev_res0[g]);
+        if (e == cudaSuccess) e = cudaEventCreate(&m->ev_resolved[g]);
+        if (e != cudaSuccess) { rtb200_multi_destroy(m); return fail(RTB200_ERR_CUDA, std::string("rtb200_multi_create: ") + cudaGetErrorString(e)); }
+    }
+    // direct peer access between every pair of distinct devices (NVLink / NVSwitch on a B200 box)
+    for (int a = 0; a < n_devices && m->peer_ok; a++) {
+        for (int b = 0; b < n_devices; b++) {
+            if (m->device[a] == m->device[b]) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, m->device[a], m->device[b]) != cudaSuccess || !can) { m->peer_ok = false; break; }
+            cudaSetDevice(m->device[a]);
+            cudaError_t e = cudaDeviceEnablePeerAccess(m->device[b], 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+            if (e != cudaSuccess) { cudaGetLastError(); m->peer_ok = false; break; }
+        }
+    }
+    *out = m;
+    return RTB200_OK;
+}
+
+void rtb200_multi_destroy(rtb200_multi* m) {
+    if (!m) return;
+    for (int g = 0; g < m->n; g++) {
+        if (!m->ctx[g]) continue;                      // a shard rtb200_multi_create never got to
+        cudaSetDevice(m->device[g]);
+        if (m->stream[g]) { cudaStreamSynchronize(m->stream[g]); cudaStreamDestroy(m->stream[g]); }
+        if (m->ev_start[g]) cudaEventDestroy(m->ev_start[g]);
+        if (m->ev_traced[g]) cudaEventDestroy(m->ev_traced[g]);
+        if (m->ev_res0[g]) cudaEventDestroy(m->ev_res0[g]);
+        if (m->ev_resolved[g]) cudaEventDestroy(m->ev_resolved[g]);
+        cudaFree(m->accum[g]);
+    }
+    if (m->n > 0 && m->ctx[0]) {
+        cudaSetDevice(m->device[0]);
+        cudaFree(m->root_rgb8); cudaFree(m->root_sum);
+        for (int g = 0; g < m->n; g++) cudaFree(m->staging[g]);
+    }
+    for (int g = 0; g < m->n; g++) rtb200_destroy(m->ctx[g]);
+    cudaGetLastError();                                // leave no stale error behind for the next call's launch check
+    delete m;
+}
+
+int rtb200_multi_info(rtb200_multi* m, int32_t* n_shards, int32_t* peer_access) {
+    if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    if (n_shards) *n_shards = m->n;
+    if (peer_access) *peer_access = m->peer_ok ? 1 : 0;
+    return RTB200_OK;
+}
+
+int rtb200_multi_upload_scene(rtb200_multi* m, const rtb200_scene* scene) {
+    if (!m || !scene) return fail(RTB200_ERR_INVALID, "null argument");
+    for (int g = 0; g < m->n; g++) {
+        int rc = rtb200_upload_scene(m->ctx[g], scene);
+        if (rc) return rc;
+    }
+    return RTB200_OK;
+}
+
+int rtb200_multi_set_hit_mode(rtb200_multi* m, int32_t mode) {
+    if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    for (int g = 0; g < m->n; g++) {
+        int rc = rtb200_set_hit_mode(m->ctx[g], mode);
+        if (rc) return rc;
+    }
+    return RTB200_OK;
+}
+
+int rtb200_multi_set_progress(rtb200_multi* m, rtb200_progress_fn fn, void* user, int32_t interval_ms) {
+    if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    if (interval_ms < 1) interval_ms = 1;
+    for (int g = 0; g < m->n; g++) {   // the shards' kernels publish their queue heads; the polling is done by rtb200_multi_render
+        int rc = rtb200_set_progress(m->ctx[g], fn ? multi_noop_progress : nullptr, nullptr, interval_ms);
+        if (rc) return rc;
+    }
+    m->progress_cb = fn; m->progress_user = user; m->progress_interval_ms = interval_ms;
+    return RTB200_OK;
+}
+
+int rtb200_multi_render(rtb200_multi* m, const rtb200_camera* camera, const rtb200_params* params, int32_t row_groups, uint8_t* rgb8_out,
+                        float* linear_rgba_out, rtb200_stats* stats) {
+    if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    int rc = validate_params(m->ctx[0], camera, params);
+    if (rc) return rc;
+    const int N = m->n;
+    if (row_groups < 1 || N % row_groups) return fail(RTB200_ERR_INVALID, "row_groups must divide the number of shards (" + std::to_string(N) + ")");
+    const int R = row_groups, S = N / R;
+    if (params->row_stride > 1) return fail(RTB200_ERR_INVALID, "rtb200_multi_render shards the rows itself: row_stride must be 0 or 1");
+    if (R > 1 && params->row_begin != 0) return fail(RTB200_ERR_INVALID, "row_begin must be 0 when row_groups > 1");
+    for (int g = 1; g < N; g++)
+        if (!m->ctx[g]->d_spheres || m->ctx[g]->n_spheres != m->ctx[0]->n_spheres) return fail(RTB200_ERR_STATE, "scene not uploaded to every shard (rtb200_multi_upload_scene)");
+    auto t0 = std::chrono::steady_clock::now();
+    const int W = camera->image_width, H = camera->image_height;
+    const size_t n_pix = (size_t)W * H;
+    rc = multi_ensure_buffers(m, n_pix, linear_rgba_out != nullptr);
+    if (rc) return rc;
+    const bool full_rows = params->row_begin == 0 && params->row_end == H;
+    const int n_samples = params->sample_end - params->sample_begin;
+    // ---- every shard's trace, queued back to back by this one thread ----
+    for (int g = 0; g < N; g++) {
+        const int gr = g / S, gs = g % S;
+        rtb200_params p = *params;
+        p.sample_begin = params->sample_begin + (int)((long long)n_samples * gs / S);
+        p.sample_end = params->sample_begin + (int)((long long)n_samples * (gs + 1) / S);
+        p.row_begin = params->row_begin + gr;
+        if (p.row_begin > p.row_end) p.row_begin = p.row_end;
+        p.row_stride = R;
+        CU_TRY(cudaSetDevice(m->device[g]));
+        if (!full_rows) CU_TRY(cudaMemsetAsync(m->accum[g], 0, n_pix * sizeof(float4), m->stream[g]));
+        CU_TRY(cudaEventRecord(m->ev_start[g], m->stream[g]));
+        rc = launch_trace(m->ctx[g], camera, &p, m->accum[g], m->stream[g]);
+        if (rc) return rc;
+        CU_TRY(cudaEventRecord(m->ev_traced[g], m->stream[g]));
+    }
+    // ---- progress (optional): poll the shards' published queue heads until the last trace has finished ----
+    if (m->progress_cb) {
+        unsigned long long total = 0;
+        for (int g = 0; g < N; g++) total += m->ctx[g]->items_total;
+        unsigned long long seen = 0;
+        auto last = std::chrono::steady_clock::now();
+        for (;;) {
+            bool done = true;
+            for (int g = 0; g < N && done; g++) {
+                cudaError_t q = cudaEventQuery(m->ev_traced[g]);
+                if (q == cudaErrorNotReady) done = false;
+                else if (q != cudaSuccess) { CU_TRY(q); }
+            }
+            if (done) break;
+            std::this_thread::sleep_for(std::chrono::microseconds(500));
+            auto now = std::chrono::steady_clock::now();
+            if (std::chrono::duration<double, std::milli>(now - last).count() < (double)m->progress_interval_ms) continue;
+            last = now;
+            unsigned long long claimed = 0;
+            for (int g = 0; g < N; g++) {
+                unsigned long long c = m->ctx[g]->h_progress ? *reinterpret_cast<volatile unsigned long long*>(m->ctx[g]->h_progress) : 0ull;
+                claimed += c < m->ctx[g]->items_total ? c : m->ctx[g]->items_total;
+            }
+            if (claimed < seen) claimed = seen;
+            seen = claimed;
+            m->progress_cb(m->progress_user, claimed, total, std::chrono::duration<double>(now - t0).count());
+        }
+        m->progress_cb(m->progress_user, total, total, std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+    }
+    // ---- fused reduce + resolve: shard g owns the pixel slice [b_g, b_{g+1}) (4-pixel aligned), reads all shards' sums ----
+    const int spp = params->samples_per_pixel;
+    float4* sum_dst = linear_rgba_out ? m->root_sum : nullptr;
+    if (m->peer_ok) {
+        std::vector<const void*> ptrs((size_t)N);
+        for (int k = 0; k < N; k++) ptrs[k] = m->accum[k];
+        for (int g = 0; g < N; g++) {
+            const long long b0 = g == 0 ? 0 : (long long)(n_pix * (size_t)g / N) & ~3LL;
+            const long long b1 = g == N - 1 ? (long long)n_pix : (long long)(n_pix * (size_t)(g + 1) / N) & ~3LL;
+            CU_TRY(cudaSetDevice(m->device[g]));
+            for (int k = 0; k < N; k++) if (k != g) CU_TRY(cudaStreamWaitEvent(m->stream[g], m->ev_traced[k], 0));
+            CU_TRY(cudaEventRecord(m->ev_res0[g], m->stream[g]));
+            rc = rtb200_resolve_grid_sum_device(m->ctx[g], ptrs.data(), R, S, W, b0, b1, spp, m->root_rgb8, sum_dst, m->stream[g]);
+            if (rc) return rc;
+            CU_TRY(cudaEventRecord(m->ev_resolved[g], m->stream[g]));
+        }
+        CU_TRY(cudaSetDevice(m->device[0]));
+        for (int k = 1; k < N; k++) CU_TRY(cudaStreamWaitEvent(m->stream[0], m->ev_resolved[k], 0));
+    } else {
+        // no peer access: bring the partial images to the root device, resolve everything there
+        CU_TRY(cudaSetDevice(m->device[0]));
+        std::vector<const void*> ptrs((size_t)N);
+        ptrs[0] = m->accum[0];
+        for (int k = 1; k < N; k++) {
+            CU_TRY(cudaStreamWaitEvent(m->stream[0], m->ev_traced[k], 0));
+            CU_TRY(cudaMemcpyPeerAsync(m->staging[k], m->device[0], m->accum[k], m->device[k], n_pix * sizeof(float4), m->stream[0]));
+            ptrs[k] = m->staging[k];
+        }
+        CU_TRY(cudaEventRecord(m->ev_res0[0], m->stream[0]));
+        rc = rtb200_resolve_grid_sum_device(m->ctx[0], ptrs.data(), R, S, W, 0, (long long)n_pix, spp, m->root_rgb8, sum_dst, m->stream[0]);
+        if (rc) return rc;
+        CU_TRY(cudaEventRecord(m->ev_resolved[0], m->stream[0]));
+    }
+    if (rgb8_out) CU_TRY(cudaMemcpyAsync(rgb8_out, m->root_rgb8, n_pix * 3, cudaMemcpyDeviceToHost, m->stream[0]));
+    if (linear_rgba_out) CU_TRY(cudaMemcpyAsync(linear_rgba_out, m->root_sum, n_pix * sizeof(float4), cudaMemcpyDeviceToHost, m->stream[0]));
+    CU_TRY(cudaStreamSynchronize(m->stream[0]));
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        for (int g = 0; g < N; g++) {
+            CU_TRY(cudaSetDevice(m->device[g]));
+            CU_TRY(cudaStreamSynchronize(m->stream[g]));
+            unsigned long long cnt[2] = {0, 0};
+            CU_TRY(cudaMemcpy(cnt, m->ctx[g]->d_counters, sizeof(cnt), cudaMemcpyDeviceToHost));
+            stats->paths += cnt[0]; stats->segments += cnt[1];
+            float ms = 0.f;
+            CU_TRY(cudaEventElapsedTime(&ms, m->ev_start[g], m->ev_traced[g]));
+            if (ms > stats->trace_ms) stats->trace_ms = ms;
+            if (m->peer_ok || g == 0) {
+                CU_TRY(cudaEventElapsedTime(&ms, m->ev_res0[g], m->ev_resolved[g]));
+                if (ms > stats->resolve_ms) stats->resolve_ms = ms;
+            }
+        }
+        stats->sphere_tests = stats->segments * (unsigned long long)m->ctx[0]->n_spheres;
+        stats->pixels_rendered = (uint64_t)(params->row_end - params->row_begin) * W;              // RenderStat::new, src/renderer.rs:385
+        stats->seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        stats->pixels_per_second = stats->seconds > 0 ? (double)stats->pixels_rendered / stats->seconds : 0.0;
+    }
     return RTB200_OK;
 }
 

@@ -273,3 +273,89 @@ class CudaRenderer(Renderer):
         p, s = C.c_uint64(), C.c_uint64()
         _abi.check(_abi.lib.rtb200_read_counters(self._ctx, C.byref(p), C.byref(s)))
         return p.value, s.value
+
+
+class MultiGpuRenderer(Renderer):
+    """Renderer::render over the GPUs of one box in ONE call (rtb200_multi, include/rtb200.h): the reference's `render`
+    owns its worker threads (src/renderer.rs:272-296, :367-369); this one owns its devices — one host thread queues every
+    shard's trace kernel, the fused reduce+resolve kernels read the partial sums over NVLink peer memory, and the image
+    comes back in the caller's host buffer.  No torch, no NCCL, no other process.
+
+    devices: device indices, one shard each (a device may repeat); None = every visible device.
+    row_groups: 1 = sample-range sharding (default), len(devices) = interleaved-scanline sharding, in between = the
+    row groups x sample groups grid (tile + sample)."""
+
+    def __init__(self, devices=None, seed: int = 1, row_groups: int = 1, n_devices: Optional[int] = None):
+        self._m = C.c_void_p()
+        if devices is None:
+            if n_devices is None:
+                raise ValueError("give devices=[...] or n_devices=N")
+            arr, n = None, int(n_devices)
+        else:
+            devices = [int(d) for d in devices]
+            arr, n = (C.c_int32 * len(devices))(*devices), len(devices)
+        _abi.check(_abi.lib.rtb200_multi_create(arr, n, C.byref(self._m)))
+        self.n_shards = n
+        self.seed = int(seed)
+        self.row_groups = int(row_groups)
+        self.flags = 0
+        self._scene = None
+        self._keep = None
+        self._progress_c = None
+
+    def close(self) -> None:
+        if getattr(self, "_m", None) is not None and self._m:
+            _abi.lib.rtb200_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> dict:
+        n, peer = C.c_int32(), C.c_int32()
+        _abi.check(_abi.lib.rtb200_multi_info(self._m, C.byref(n), C.byref(peer)))
+        return {"n_shards": n.value, "peer_access": bool(peer.value)}
+
+    def upload_scene(self, scene: Scene) -> None:
+        sc, keep = scene.to_abi()
+        _abi.check(_abi.lib.rtb200_multi_upload_scene(self._m, C.byref(sc)))
+        self._scene, self._keep = scene, keep
+
+    def set_hit_mode(self, both_roots: bool) -> None:
+        _abi.check(_abi.lib.rtb200_multi_set_hit_mode(self._m, 1 if both_roots else 0))
+
+    def set_progress(self, callback=None, interval_ms: int = 100) -> None:
+        if callback is None:
+            self._progress_c = None
+            _abi.check(_abi.lib.rtb200_multi_set_progress(self._m, None, None, int(interval_ms)))
+            return
+        proto = C.CFUNCTYPE(None, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double)
+        self._progress_c = proto(lambda user, done, total, secs: callback(int(done), int(total), float(secs)))
+        _abi.check(_abi.lib.rtb200_multi_set_progress(self._m, C.cast(self._progress_c, C.c_void_p), None, int(interval_ms)))
+
+    def render(self, max_bounces: int, samples_per_pixel: int, scene: Scene, camera: Camera, *, want_linear: bool = False,
+               sample_range=None, row_range=None, out: Optional[np.ndarray] = None, row_groups: Optional[int] = None):
+        """Renderer::render (src/renderer.rs:38-40) on all shards.  Same returns as CudaRenderer.render; the linear image
+        is the SUM over all shards as the reduce kernel formed it."""
+        if self._scene is not scene:
+            self.upload_scene(scene)
+        W, H = camera.image_width(), camera.image_height()
+        if out is not None:
+            if out.shape != (H, W, 3) or out.dtype != np.uint8 or not out.flags.c_contiguous:
+                raise ValueError("out must be a C-contiguous [H,W,3] uint8 array")
+            img = out
+        else:
+            img = np.empty((H, W, 3), dtype=np.uint8)
+        lin = np.empty((H, W, 4), dtype=np.float32) if want_linear else None
+        s0, s1 = sample_range if sample_range is not None else (0, samples_per_pixel)
+        r0, r1 = row_range if row_range is not None else (0, H)
+        p = _abi.Params(int(max_bounces), int(samples_per_pixel), self.seed & 0xFFFFFFFFFFFFFFFF, int(s0), int(s1), int(r0), int(r1), int(self.flags), 1)
+        st = _abi.Stats()
+        _abi.check(_abi.lib.rtb200_multi_render(self._m, C.byref(camera.abi), C.byref(p), int(row_groups if row_groups is not None else self.row_groups),
+                                                _ptr(img), _ptr(lin), C.byref(st)))
+        stat = RenderStat(st.seconds, st.pixels_rendered, st.pixels_per_second, st.paths, st.segments, st.sphere_tests,
+                          st.trace_ms, st.resolve_ms, st.d2h_ms)
+        return (img, lin, stat) if want_linear else (img, stat)
