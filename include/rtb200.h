@@ -272,6 +272,16 @@ int rtb200_multi_set_progress(rtb200_multi* m, rtb200_progress_fn fn, void* user
 int rtb200_multi_render(rtb200_multi* m, const rtb200_camera* camera, const rtb200_params* params, int32_t row_groups,
                         uint8_t* rgb8_out, float* linear_rgba_out, rtb200_stats* stats);
 
+/* Stream-ordered barrier between the ranks of a one-process-per-GPU job, through peer memory (no NCCL call, no host round
+ * trip): flag_ptrs[k] = rank k's flag array (RTB200_MAX_PEERS uint32 words from rtb200_device_alloc, zero-initialised; the
+ * caller's own and the peers' opened with rtb200_ipc_open).  The kernel publishes `epoch` (the caller increases it by one per
+ * barrier) into slot my_rank of every array and waits until every slot of its own array has reached it; work queued on
+ * `stream` after this call starts only when every rank's stream has reached its barrier of the same epoch, and sees what the
+ * peers wrote before theirs.  The wait is bounded by timeout_s (<= 0: 20 s): a missing rank makes the kernel trap — the
+ * process fails loudly instead of hanging. */
+int rtb200_peer_barrier_device(rtb200_ctx* ctx, void* const* flag_ptrs, int32_t n_peers, int32_t my_rank, uint32_t epoch,
+                               double timeout_s, void* stream);
+
 /* rtb200_resolve_grid_device that also stores the summed float4 image for its pixel range into sum_dev (a WHOLE-image float4
  * buffer, local or a peer's; null = not wanted): how a caller of the multi-GPU path gets the linear image before quantisation. */
 int rtb200_resolve_grid_sum_device(rtb200_ctx* ctx, const void* const* accum_ptrs, int32_t row_groups, int32_t sample_groups,
@@ -294,6 +304,14 @@ int rtb200_set_hit_mode(rtb200_ctx* ctx, int32_t mode);
 
 /* Number of kernel launches this context has issued since creation (trace, resolve, intersect, probe). */
 int64_t rtb200_launch_count(rtb200_ctx* ctx);
+
+/* The trace kernel ALONE (without the combine pass that follows it when the sample range is split): average device time of
+ * the last n_last launches on this context (<= 0 or more than recorded: all of the last 64), from CUDA events recorded on
+ * the launching stream around each launch; *kernel_name = the variant the last launch ran; *sample_splits = K of the last
+ * launch: each pixel's sample range was traced as K contiguous sub-ranges whose FP32 partial sums were added in order
+ * (what a checker needs to reproduce the summation bit for bit).  Any pointer may be null.  Waits for those launches. */
+int rtb200_trace_kernel_stats(rtb200_ctx* ctx, int32_t n_last, double* avg_ms, int32_t* n_used, const char** kernel_name,
+                              int32_t* sample_splits);
 
 /* Self-check of the sweep's conservative FP32 filters, on the device, with the arithmetic the render kernels run.  The
  * reference tests every (ray, sphere) pair with Sphere::hit_packed's discriminant (src/objects.rs:252-259); the sweeps run

@@ -11,39 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtb200.so")
 
-OK, ERR_INVALID, ERR_CUDA, ERR_STATE = 0, -1, -2, -3
-LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
-
-
-class Material(C.Structure):
-    _fields_ = [("kind", C.c_int32), ("hollow", C.c_int32), ("albedo", C.c_double * 3), ("param", C.c_double)]
-
-
-class Sphere(C.Structure):
-    _fields_ = [("center", C.c_double * 3), ("radius", C.c_double), ("material", C.c_int32), ("_pad", C.c_int32)]
-
-
-class Scene(C.Structure):
-    _fields_ = [("spheres", C.POINTER(Sphere)), ("n_spheres", C.c_int32), ("materials", C.POINTER(Material)),
-                ("n_materials", C.c_int32)]
-
-
-class Camera(C.Structure):
-    _fields_ = [("image_width", C.c_int32), ("image_height", C.c_int32), ("center", C.c_double * 3),
-                ("viewport_upper_left_corner", C.c_double * 3), ("viewport_u", C.c_double * 3),
-                ("viewport_v", C.c_double * 3), ("defocus_u", C.c_double * 3), ("defocus_v", C.c_double * 3)]
-
-
-class Params(C.Structure):
-    _fields_ = [("max_bounces", C.c_int32), ("samples_per_pixel", C.c_int32), ("seed", C.c_uint64),
-                ("sample_begin", C.c_int32), ("sample_end", C.c_int32), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("flags", C.c_int32), ("row_stride", C.c_int32)]
-
-
-class Stats(C.Structure):
-    _fields_ = [("seconds", C.c_double), ("pixels_rendered", C.c_uint64), ("pixels_per_second", C.c_double),
-                ("paths", C.c_uint64), ("segments", C.c_uint64), ("sphere_tests", C.c_uint64),
-                ("trace_ms", C.c_double), ("resolve_ms", C.c_double), ("h2d_ms", C.c_double), ("d2h_ms", C.c_double)]
+from ._abi_types import (OK, ERR_INVALID, ERR_CUDA, ERR_STATE, LAMBERTIAN, METAL, DIELECTRIC, Material, Sphere, Scene, Camera, Params, Stats)  # noqa: F401
 
 
 # every symbol include/rtb200.h declares: name -> (restype, argtypes)
@@ -73,6 +41,7 @@ SYMBOLS = {
     "rtb200_resolve_peers_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_resolve_grid_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_resolve_grid_sum_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int64, C.c_int32, _P, _P, _P]),
+    "rtb200_peer_barrier_device": (C.c_int, [_P, C.POINTER(_P), C.c_int32, C.c_int32, C.c_uint32, C.c_double, _P]),
     "rtb200_multi_create": (C.c_int, [C.POINTER(C.c_int32), C.c_int32, C.POINTER(_P)]),
     "rtb200_multi_destroy": (None, [_P]),
     "rtb200_multi_info": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
@@ -82,6 +51,7 @@ SYMBOLS = {
     "rtb200_multi_render": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), C.c_int32, _P, _P, C.POINTER(Stats)]),
     "rtb200_read_counters": (C.c_int, [_P, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "rtb200_launch_count": (C.c_int64, [_P]),
+    "rtb200_trace_kernel_stats": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_char_p), C.POINTER(C.c_int32)]),
     "rtb200_set_hit_mode": (C.c_int32, [_P, C.c_int32]),
     "rtb200_set_progress": (C.c_int32, [_P, C.c_void_p, C.c_void_p, C.c_int32]),
     "rtb200_fp32_peak": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

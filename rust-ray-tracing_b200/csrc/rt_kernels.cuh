@@ -1292,6 +1292,37 @@ __global__ void __launch_bounds__(256) k_resolve_peers(const __grid_constant__ P
     }
 }
 
+// ---- peer barrier: a stream-ordered barrier between the GPUs of one box, through peer memory ------------------------------
+// One process per GPU, each with a flag array of n_peers words that every peer has mapped (CUDA IPC).  Rank r's kernel
+// publishes `epoch` into slot r of EVERY rank's array (peer stores over NVLink, after a system-scope fence so that everything
+// the stream wrote before — the partial framebuffer — is visible first), then waits until all slots of its OWN array have
+// reached `epoch`.  Kernels queued behind it on the stream therefore start only after every rank has finished what it queued
+// before its barrier: what the exchange needs before the reduce (all traces done) and after it (all slices landed) — without
+// a host round trip and without an NCCL call per step.  A rank that never arrives would hang the others, so the wait is
+// bounded: after timeout_ns the kernel traps and the next CUDA call of that process fails loudly.
+struct BarrierPtrs { unsigned int* p[16]; };
+
+__global__ void __launch_bounds__(32) k_peer_barrier(const __grid_constant__ BarrierPtrs flags, int n_peers, int my_rank, unsigned int epoch,
+                                                     unsigned long long timeout_ns) {
+    const int g = (int)threadIdx.x;
+    if (g >= n_peers) return;
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags.p[g] + my_rank), "r"(epoch) : "memory");
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    const unsigned int* mine = flags.p[my_rank] + g;
+    for (;;) {
+        unsigned int v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+        if ((int)(v - epoch) >= 0) break;                     // epochs only grow (wrap-safe comparison)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) __trap();
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
 // ---- filter self-check: the conservative filters against the exact test, ON THE DEVICE --------------------------------
 // The parity of every sweep rests on two FP32 filters never rejecting a pair the exact (f64) test accepts.  This kernel
 // brute-forces that property with the arithmetic that actually runs: the device builds of make_filter / make_slab_ray

@@ -83,6 +83,12 @@ struct rtb200_ctx {
     void* d_rays = nullptr; size_t rays_bytes = 0;
     float* d_probe = nullptr;
     cudaEvent_t ev[4]{};
+    // the trace kernel ALONE (without k_combine), per launch: a ring of event pairs recorded inside launch_trace
+    static constexpr int TRACE_RING = 64;
+    cudaEvent_t ev_trace[TRACE_RING][2]{};
+    int64_t trace_launches = 0;                        // trace kernels launched so far (ring index = count % TRACE_RING)
+    const char* last_kernel = "";                      // the trace-kernel variant of the last launch
+    int last_splits = 1;                               // K of the last launch: sample sub-ranges per pixel (partial planes summed in plane order)
     int64_t launches = 0;
     size_t max_optin_smem = 0;
     bool attrs_set = false;
@@ -278,13 +284,20 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         ps->rp_min = ctx->slab_rp_min;
         std::memcpy(ps->s1, ctx->h_slab.data(), ctx->h_slab.size() * sizeof(float));
     };
+    cudaEvent_t* ring = ctx->ev_trace[ctx->trace_launches % rtb200_ctx::TRACE_RING];
+    if (!ring[0]) { CU_TRY(cudaEventCreate(&ring[0])); CU_TRY(cudaEventCreate(&ring[1])); }
+    CU_TRY(cudaEventRecord(ring[0], st));
+    ctx->last_splits = splits;
     if (streamed) {
+        ctx->last_kernel = "k_trace_paths_g<640,2> (two-stage, stage-1 triples streamed per warp from global memory)";
         launch_streamed();
     } else if (two_stage && P.n_spheres <= 512) {
+        ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsS<512>> (two-stage, stage-1 triples in kernel parameter space)";
         auto* ps = reinterpret_cast<PS512*>(ctx->h_params.data());
         fill_s(ps);
         k_s512<<<sms * 4, VT, smem_v, st>>>(*ps);
     } else if (two_stage) {
+        ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsS<768>> (two-stage, stage-1 triples in kernel parameter space)";
         auto* ps = reinterpret_cast<PS768*>(ctx->h_params.data());
         fill_s(ps);
         k_s768<<<sms * 4, VT, smem_v, st>>>(*ps);
@@ -293,26 +306,38 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
         const size_t smem_slr = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
-        if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) k_slr<<<sms, LRT, smem_slr, st>>>(pl);
-        else k_sl<<<sms, LT, smem_sl, st>>>(pl);
+        if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) {
+            ctx->last_kernel = "k_trace_paths_l<640,2> (two-stage, stage-1 triples staged in shared memory, path state in registers)";
+            k_slr<<<sms, LRT, smem_slr, st>>>(pl);
+        } else {
+            ctx->last_kernel = "k_trace_paths_v<512,1,2,8,TraceParamsL> (two-stage, stage-1 triples and path state in shared memory)";
+            k_sl<<<sms, LT, smem_sl, st>>>(pl);
+        }
     } else if (use_v && P.n_spheres <= 512) {
+        ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsV<512>> (one-stage filter sweep from kernel parameter space)";
         auto* pv = reinterpret_cast<PV512*>(ctx->h_params.data());
         pv->b = P;
         std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
         k_v512<<<sms * 4, VT, smem_v, st>>>(*pv);
     } else if (use_v) {
+        ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsV<1024>> (one-stage filter sweep from kernel parameter space)";
         auto* pv = reinterpret_cast<PV1024*>(ctx->h_params.data());
         pv->b = P;
         std::memcpy(pv->flt, ctx->h_filter.data(), (size_t)P.n_spheres * sizeof(float4));
         k_v1024<<<sms * 4, VT, smem_v, st>>>(*pv);
     } else if ((smem_m1 + 1024) * 4 <= per_sm) {
+        ctx->last_kernel = "k_trace_paths<256,4,1,6> (one-stage filter sweep, spheres staged in shared memory)";
         k_m1<<<sms * 4, SMALL_THREADS, smem_m1, st>>>(P);
     } else if (smem_l1 <= ctx->max_optin_smem) {
+        ctx->last_kernel = "k_trace_paths<1024,1,1,6> (one-stage filter sweep, spheres staged in shared memory)";
         k_l1<<<sms, LARGE_THREADS, smem_l1, st>>>(P);
     } else {
+        ctx->last_kernel = "k_trace_paths_g<640,2> (two-stage, stage-1 triples streamed per warp from global memory)";
         launch_streamed();                                 // nothing else holds the scene
     }
     CU_TRY(cudaGetLastError());
+    CU_TRY(cudaEventRecord(ring[1], st));
+    ctx->trace_launches++;
     ctx->launches++;
     if (splits > 1) {
         int blocks = (int)((n_pix + 255) / 256);
@@ -394,6 +419,7 @@ void rtb200_destroy(rtb200_ctx* c) {
     cudaFree(c->d_scene); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    for (auto& pr : c->ev_trace) for (auto& e : pr) if (e) cudaEventDestroy(e);
     if (c->h_progress) cudaFreeHost(c->h_progress);
     delete c;
 }
@@ -803,6 +829,23 @@ int rtb200_resolve_peers_device(rtb200_ctx* ctx, const void* const* accum_ptrs, 
     return rtb200_resolve_grid_device(ctx, accum_ptrs, 1, n_peers, 1, pixel_begin, pixel_end, samples_per_pixel, rgb8_dev, stream);
 }
 
+int rtb200_peer_barrier_device(rtb200_ctx* ctx, void* const* flag_ptrs, int32_t n_peers, int32_t my_rank, uint32_t epoch, double timeout_s, void* stream) {
+    if (!ctx || !flag_ptrs) return fail(RTB200_ERR_INVALID, "null argument");
+    if (n_peers < 1 || n_peers > RTB200_MAX_PEERS || my_rank < 0 || my_rank >= n_peers) return fail(RTB200_ERR_INVALID, "bad peer count or rank");
+    rtb::BarrierPtrs bp;
+    for (int k = 0; k < RTB200_MAX_PEERS; k++) bp.p[k] = nullptr;
+    for (int k = 0; k < n_peers; k++) {
+        if (!flag_ptrs[k]) return fail(RTB200_ERR_INVALID, "null flag pointer");
+        bp.p[k] = static_cast<unsigned int*>(flag_ptrs[k]);
+    }
+    if (!(timeout_s > 0.0)) timeout_s = 20.0;
+    CU_TRY(cudaSetDevice(ctx->device));
+    rtb::k_peer_barrier<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(bp, n_peers, my_rank, epoch, (unsigned long long)(timeout_s * 1e9));
+    CU_TRY(cudaGetLastError());
+    ctx->launches++;
+    return RTB200_OK;
+}
+
 int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
     CU_TRY(cudaSetDevice(ctx->device));
@@ -814,6 +857,26 @@ int rtb200_read_counters(rtb200_ctx* ctx, uint64_t* paths, uint64_t* segments) {
 }
 
 int64_t rtb200_launch_count(rtb200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int rtb200_trace_kernel_stats(rtb200_ctx* ctx, int32_t n_last, double* avg_ms, int32_t* n_used, const char** kernel_name, int32_t* sample_splits) {
+    if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (kernel_name) *kernel_name = ctx->last_kernel;
+    if (sample_splits) *sample_splits = ctx->last_splits;
+    int64_t n = ctx->trace_launches < rtb200_ctx::TRACE_RING ? ctx->trace_launches : rtb200_ctx::TRACE_RING;
+    if (n_last > 0 && n_last < n) n = n_last;
+    double sum = 0.0;
+    CU_TRY(cudaSetDevice(ctx->device));
+    for (int64_t k = 0; k < n; k++) {
+        cudaEvent_t* pr = ctx->ev_trace[(ctx->trace_launches - 1 - k) % rtb200_ctx::TRACE_RING];
+        CU_TRY(cudaEventSynchronize(pr[1]));
+        float ms = 0.f;
+        CU_TRY(cudaEventElapsedTime(&ms, pr[0], pr[1]));
+        sum += ms;
+    }
+    if (avg_ms) *avg_ms = n > 0 ? sum / (double)n : 0.0;
+    if (n_used) *n_used = (int32_t)n;
+    return RTB200_OK;
+}
 
 int rtb200_set_progress(rtb200_ctx* ctx, rtb200_progress_fn fn, void* user, int32_t interval_ms) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "null context");

@@ -16,9 +16,10 @@ Two exchanges are implemented (ShardedRenderer(exchange=...)):
   "p2p"  (default where it works) — NVLink peer memory, no reduce pass: every rank's accumulation image is a plain
          cudaMalloc buffer exported with CUDA IPC; after the trace, rank g runs ONE kernel (rtb200_resolve_peers_device)
          that, for its slice of the pixels, loads the partial sums of ALL ranks straight from peer memory, adds them in
-         rank order (deterministic), quantises, and stores the RGB8 slice directly into rank dst's image.  The only
-         torch.distributed calls are two 4-byte all-reduces used as stream-ordered barriers (before: every trace has
-         finished; after: every slice has landed).
+         rank order (deterministic), quantises, and stores the RGB8 slice directly into rank dst's image.  The two
+         stream-ordered barriers a step needs (before: every trace has finished; after: every slice has landed) are
+         peer-memory flag kernels too (rtb200_peer_barrier_device): a step makes NO torch.distributed / NCCL call
+         (barrier="nccl" keeps the earlier form, two 4-byte all-reduces, as the baseline).
   "nccl" — reduce(SUM) of the float4 image onto dst, then the resolve kernel there (the baseline; also the fallback
          when IPC / peer access is unavailable).
 
@@ -61,9 +62,13 @@ class CudaTracer:
     def new_peer_exchange(self, dist, group, world, rank, height, width):
         return PeerExchange(self, dist, group, world, rank, height, width)
 
-    def resolve_grid(self, accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr):
+    def resolve_grid(self, accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr, sum_ptr=0):
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
-        self.r.resolve_grid_device(accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr, stream)
+        self.r.resolve_grid_sum_device(accum_ptrs, row_groups, sample_groups, width, pixel_begin, pixel_end, spp_total, rgb8_ptr, sum_ptr, stream)
+
+    def peer_barrier(self, flag_ptrs, rank, epoch):
+        stream = self.torch.cuda.current_stream(self.device).cuda_stream
+        self.r.peer_barrier_device(flag_ptrs, rank, epoch, stream)
 
     def resolve_peers(self, accum_ptrs, pixel_begin, pixel_end, spp_total, rgb8_ptr):
         stream = self.torch.cuda.current_stream(self.device).cuda_stream
@@ -104,42 +109,58 @@ class PeerExchange:
         self.tracer, self.world, self.rank, self.H, self.W = tracer, world, rank, height, width
         r = tracer.r
         n_pix = height * width
+        self.dist, self.group = dist, group
         self.accum = DeviceBuffer(r.device_alloc(n_pix * 16), (height, width, 4), "<f4")
         self.rgb8 = DeviceBuffer(r.device_alloc(n_pix * 3 + 16), (height, width, 3), "|u1")
-        mine = torch.tensor(list(r.ipc_export(self.accum.ptr)) + list(r.ipc_export(self.rgb8.ptr)), dtype=torch.uint8, device=tracer.device)
+        self.sum = DeviceBuffer(r.device_alloc(n_pix * 16), (height, width, 4), "<f4")       # the summed linear image (on request; dst's is used)
+        self.flags = DeviceBuffer(r.device_alloc(64), (16,), "<u4")                           # peer-barrier slots (zero-initialised)
+        self.epoch = 0
+        own = (self.accum, self.rgb8, self.sum, self.flags)
+        mine = torch.tensor([x for b in own for x in r.ipc_export(b.ptr)], dtype=torch.uint8, device=tracer.device)
         every = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(every, mine, group=group)
-        self.peer_accum, self.peer_rgb8, self._opened = [], [], []
+        self.peer_accum, self.peer_rgb8, self.peer_sum, self.peer_flags, self._opened = [], [], [], [], []
+        lists = (self.peer_accum, self.peer_rgb8, self.peer_sum, self.peer_flags)
         ok = 1
         for g, h in enumerate(every):
             if g == rank:
-                self.peer_accum.append(self.accum.ptr)
-                self.peer_rgb8.append(self.rgb8.ptr)
+                for lst, b in zip(lists, own):
+                    lst.append(b.ptr)
                 continue
             hb = bytes(h.cpu().tolist())
-            try:
-                a = r.ipc_open(hb[:64])
-                self._opened.append(a)
-                b = r.ipc_open(hb[64:])
-                self._opened.append(b)
-                self.peer_accum.append(a)
-                self.peer_rgb8.append(b)
-            except Exception:
-                ok = 0
-                self.peer_accum.append(0)
-                self.peer_rgb8.append(0)
+            for k, lst in enumerate(lists):
+                try:
+                    ptr = r.ipc_open(hb[64 * k: 64 * (k + 1)])
+                    self._opened.append(ptr)
+                    lst.append(ptr)
+                except Exception:
+                    ok = 0
+                    lst.append(0)
         flag = torch.tensor([ok], dtype=torch.int32, device=tracer.device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
         self.usable = bool(flag.item())
 
+    def barrier(self):
+        """Stream-ordered barrier over peer-memory flags (no NCCL call): see rtb200_peer_barrier_device."""
+        self.epoch += 1
+        self.tracer.peer_barrier(self.peer_flags, self.rank, self.epoch)
+
     def close(self):
+        """Collective: every rank closes its mappings of the peers' buffers, THEN (after a barrier and a device sync) frees
+        its own exported buffers — freeing an exported allocation while an importer still has it mapped is undefined."""
         for p in self._opened:
             try:
                 self.tracer.r.ipc_close(p)
             except Exception:
                 pass
         self._opened = []
-        for b in (self.accum, self.rgb8):
+        try:
+            self.tracer.torch.cuda.synchronize(self.tracer.device)
+            if self.dist.is_initialized():
+                self.dist.barrier(group=self.group)
+        except Exception:
+            pass
+        for b in (self.accum, self.rgb8, self.sum, self.flags):
             if b is not None and b.ptr:
                 self.tracer.r.device_free(b.ptr)
                 b.ptr = 0
@@ -151,13 +172,17 @@ class ShardedRenderer:
     Every rank calls render(); rank `dst` gets the RGB8 image, the others get None.
     """
 
-    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0, exchange: str = "auto", grid=None):
+    def __init__(self, tracer, group=None, mode: str = "samples", dst: int = 0, exchange: str = "auto", grid=None, barrier: str = "flags"):
         import torch.distributed as dist
         if mode not in ("samples", "rows", "grid"):
             raise ValueError("mode must be 'samples', 'rows' or 'grid'")
         if exchange not in ("auto", "p2p", "nccl"):
             raise ValueError("exchange must be 'auto', 'p2p' or 'nccl'")
+        if barrier not in ("flags", "nccl"):
+            raise ValueError("barrier must be 'flags' (peer-memory flag kernel) or 'nccl' (4-byte all-reduce)")
         self.exchange = exchange
+        self.barrier = barrier
+        self.want_sum = False     # p2p exchange: also form the summed linear image on dst (last_sum(); costs 33 MB of peer stores at 1080p)
         self._peer = None
         self.on_trace = None      # optional callback(phase): phase 0 just before, 1 just after the trace kernel is queued (timing hooks)
         self.dist = dist
@@ -220,9 +245,29 @@ class ShardedRenderer:
         return "p2p" if self._peer is not None else ("none" if self.world == 1 else "nccl")
 
     def _stream_barrier(self):
-        """Stream-ordered barrier: a 4-byte all-reduce.  It starts after this rank's queued kernels and the kernels queued
-        after it start only when every rank has reached it."""
-        self.dist.all_reduce(self._flag, group=self.group)
+        """Stream-ordered barrier: the kernels queued after it start only when every rank has finished what it queued before
+        its own.  Default: the peer-memory flag kernel; barrier="nccl": a 4-byte all-reduce."""
+        if self.barrier == "flags" and self._peer is not None and hasattr(self.tracer, "peer_barrier"):
+            self._peer.barrier()
+        else:
+            self.dist.all_reduce(self._flag, group=self.group)
+
+    def last_sum(self):
+        """p2p exchange with want_sum: the summed linear image [H,W,4] (device tensor) of the last render on dst, else None."""
+        if self._peer is None or not self.want_sum or self.rank != self.dst:
+            return None
+        return self.tracer.torch.as_tensor(self._peer.sum, device=self.tracer.device)
+
+    def close(self):
+        """Collective (every rank calls it): releases the peer-exchange buffers and mappings."""
+        if self._peer is not None:
+            self._peer.close()
+            self._peer = None
+        self._accum = None
+
+    def __del__(self):
+        # not collective-safe in general; only drops what needs no peer (close() is the orderly way)
+        self._accum = None
 
     def _render_device_p2p(self, px, max_bounces: int, spp_total: int, camera):
         H, W = px.H, px.W
@@ -234,7 +279,8 @@ class ShardedRenderer:
         R, S = self.grid
         p0, p1 = shard_range(H * W, self.world, self.rank)
         p0, p1 = (p0 + 3) // 4 * 4 if self.rank else 0, (p1 + 3) // 4 * 4 if self.rank + 1 < self.world else H * W
-        self.tracer.resolve_grid(px.peer_accum, R, S, W, min(p0, H * W), min(p1, H * W), spp_total, px.peer_rgb8[self.dst])
+        self.tracer.resolve_grid(px.peer_accum, R, S, W, min(p0, H * W), min(p1, H * W), spp_total, px.peer_rgb8[self.dst],
+                                 px.peer_sum[self.dst] if self.want_sum else 0)
         self._stream_barrier()                                   # every slice has landed in dst's image
         if self.rank == self.dst:
             return self.tracer.torch.as_tensor(px.rgb8, device=self.tracer.device)

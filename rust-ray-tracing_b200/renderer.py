@@ -269,6 +269,29 @@ class CudaRenderer(Renderer):
         _abi.check(_abi.lib.rtb200_resolve_grid_device(self._ctx, arr, int(row_groups), int(sample_groups), int(image_width), int(pixel_begin),
                                                        int(pixel_end), int(samples_per_pixel), C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
 
+    def resolve_grid_sum_device(self, accum_ptrs, row_groups: int, sample_groups: int, image_width: int, pixel_begin: int, pixel_end: int,
+                                samples_per_pixel: int, rgb8_ptr: int, sum_ptr: int, stream: int = 0) -> None:
+        """resolve_grid_device that also stores the summed float4 pixels into the whole-image buffer at sum_ptr (0: not wanted)."""
+        if len(accum_ptrs) != row_groups * sample_groups:
+            raise ValueError("accum_ptrs must hold row_groups * sample_groups pointers")
+        arr = (C.c_void_p * len(accum_ptrs))(*[C.c_void_p(p) for p in accum_ptrs])
+        _abi.check(_abi.lib.rtb200_resolve_grid_sum_device(self._ctx, arr, int(row_groups), int(sample_groups), int(image_width), int(pixel_begin),
+                                                           int(pixel_end), int(samples_per_pixel), C.c_void_p(rgb8_ptr),
+                                                           C.c_void_p(sum_ptr) if sum_ptr else None, C.c_void_p(stream)))
+
+    def peer_barrier_device(self, flag_ptrs, my_rank: int, epoch: int, stream: int = 0, timeout_s: float = 20.0) -> None:
+        """rtb200_peer_barrier_device: stream-ordered barrier between the ranks through peer-memory flags."""
+        arr = (C.c_void_p * len(flag_ptrs))(*[C.c_void_p(p) for p in flag_ptrs])
+        _abi.check(_abi.lib.rtb200_peer_barrier_device(self._ctx, arr, len(flag_ptrs), int(my_rank), int(epoch) & 0xFFFFFFFF, float(timeout_s),
+                                                       C.c_void_p(stream)))
+
+    def trace_kernel_stats(self, n_last: int = 0) -> dict:
+        """rtb200_trace_kernel_stats: the trace kernel alone — average ms of the last n_last launches (0: all recorded), the
+        kernel variant of the last launch, and its K (sample sub-ranges per pixel, summed in order)."""
+        ms, n, name, k = C.c_double(), C.c_int32(), C.c_char_p(), C.c_int32()
+        _abi.check(_abi.lib.rtb200_trace_kernel_stats(self._ctx, int(n_last), C.byref(ms), C.byref(n), C.byref(name), C.byref(k)))
+        return {"avg_ms": ms.value, "launches": n.value, "kernel": (name.value or b"").decode(), "sample_splits": k.value}
+
     def read_counters(self) -> Tuple[int, int]:
         p, s = C.c_uint64(), C.c_uint64()
         _abi.check(_abi.lib.rtb200_read_counters(self._ctx, C.byref(p), C.byref(s)))

@@ -14,7 +14,7 @@ import tomllib
 from dataclasses import dataclass, field
 from typing import Dict, List, Sequence
 
-from . import _abi
+from . import _abi_types as _abi     # structs and constants only: the library itself is loaded where it is called (Camera)
 
 
 def to_float(value) -> float:
@@ -224,9 +224,10 @@ class Camera:
     def __init__(self, image_width: int, image_height: int, focal_length: float, view_angle: float,
                  center, look_at, up, defocus_angle: float):
         """Camera::new, src/ray_tracing.rs:27-62 (evaluated by rtb200_camera_init in f64)."""
+        from . import _abi as _lib     # Camera::new runs inside the library (rtb200_camera_init): loads librtb200.so
         self.abi = _abi.Camera()
         d3 = C.c_double * 3
-        _abi.check(_abi.lib.rtb200_camera_init(C.byref(self.abi), int(image_width), int(image_height), float(focal_length),
+        _lib.check(_lib.lib.rtb200_camera_init(C.byref(self.abi), int(image_width), int(image_height), float(focal_length),
                                                float(view_angle), d3(*center), d3(*look_at), d3(*up), float(defocus_angle)))
 
     @staticmethod

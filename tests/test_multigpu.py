@@ -31,23 +31,26 @@ def _worker(rank, world, port, q, modes=(("samples", None), ("rows", None))):
         cam = rtb.Camera.default(W, H)
         r = rtb.CudaRenderer(device=rank, seed=SEED)
         tracer = dmod.CudaTracer(r, scene)
-        out = {}
+        out, lin = {}, {}
         for mode, grid in modes:
-            for exchange in ("p2p", "nccl"):
-                sr = dmod.ShardedRenderer(tracer, mode=mode, exchange=exchange, grid=grid)
+            for exchange, barrier in (("p2p", "flags"), ("p2p", "nccl"), ("nccl", "nccl")):
+                sr = dmod.ShardedRenderer(tracer, mode=mode, exchange=exchange, grid=grid, barrier=barrier)
+                sr.want_sum = True                               # p2p: the summed linear image before quantisation
                 a = sr.render(DEPTH, SPP, cam)
                 b = sr.render(DEPTH, SPP, cam)
                 assert sr.exchange_in_use() == exchange
+                key = (mode if grid is None else "%dx%d" % grid, exchange if barrier == "nccl" else "p2p-flags")
                 if rank == 0:
                     assert np.array_equal(a, b)                  # deterministic
-                    out[(mode if grid is None else "%dx%d" % grid, exchange)] = a
+                    out[key] = a
+                    if exchange == "p2p":
+                        lin[key] = sr.last_sum().cpu().numpy()
                 else:
                     assert a is None and b is None
-                if sr._peer is not None:
-                    sr._peer.close()
+                sr.close()                                       # collective: mappings closed before exported buffers are freed
         if rank == 0:
-            whole, _ = r.render(DEPTH, SPP, scene, cam)
-            q.put((out, whole))
+            whole, whole_lin, _ = r.render(DEPTH, SPP, scene, cam, want_linear=True)
+            q.put((out, whole, lin, whole_lin))
         dist.barrier()
         r.close()
     finally:
@@ -68,17 +71,22 @@ def test_two_gpu_exchanges_match_single_gpu():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    out, whole = q.get(timeout=600)
+    out, whole, lin, whole_lin = q.get(timeout=600)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
     # rows (interleaved scanlines): disjoint pixels, no summation -> identical; samples: two partial sums added -> float re-association only
-    for ex in ("p2p", "nccl"):
+    for ex in ("p2p-flags", "p2p", "nccl"):
         assert np.array_equal(out[("rows", ex)], whole)
         d = np.abs(out[("samples", ex)].astype(int) - whole.astype(int))
         assert d.max() <= 1 and (d > 0).mean() < 1e-3
-    assert np.array_equal(out[("samples", "p2p")], out[("samples", "nccl")]) or \
-        np.abs(out[("samples", "p2p")].astype(int) - out[("samples", "nccl")].astype(int)).max() <= 1
+    assert np.array_equal(out[("samples", "p2p-flags")], out[("samples", "p2p")])          # the barrier kind changes nothing
+    assert np.abs(out[("samples", "p2p")].astype(int) - out[("samples", "nccl")].astype(int)).max() <= 1
+    # the north_star's image bar at N > 1: the linear image BEFORE quantisation against the single-GPU one, 1e-4 on the mean
+    for key, img in lin.items():
+        assert np.abs(img[..., :3].astype(np.float64) - whole_lin[..., :3].astype(np.float64)).max() / SPP <= 1e-4, key
+        assert np.all(img[..., 3] == SPP), key
+    assert np.array_equal(lin[("rows", "p2p-flags")], whole_lin)
 
 
 def test_four_gpu_tile_and_sample_grid_matches_single_gpu():
@@ -97,11 +105,13 @@ def test_four_gpu_tile_and_sample_grid_matches_single_gpu():
     procs = [ctx.Process(target=_worker, args=(r, 4, port, q, modes)) for r in range(4)]
     for p in procs:
         p.start()
-    out, whole = q.get(timeout=600)
+    out, whole, lin, whole_lin = q.get(timeout=600)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    for ex in ("p2p", "nccl"):
+    for key, img in lin.items():
+        assert np.abs(img[..., :3].astype(np.float64) - whole_lin[..., :3].astype(np.float64)).max() / SPP <= 1e-4, key
+    for ex in ("p2p-flags", "p2p", "nccl"):
         assert np.array_equal(out[("4x1", ex)], whole)           # disjoint rows: no summation
         for g in ("2x2", "1x4"):                                 # partial sums added: float re-association only
             d = np.abs(out[(g, ex)].astype(int) - whole.astype(int))
