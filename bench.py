@@ -277,14 +277,14 @@ def run_ours(args):
     def max_over_ranks(x: float) -> float:
         if world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        t = torch.tensor([x], dtype=torch.float64, device=torch.device("cuda", local_rank))
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
     def sum_over_ranks(x: float) -> float:
         if world == 1:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        t = torch.tensor([x], dtype=torch.float64, device=torch.device("cuda", local_rank))
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
@@ -430,13 +430,14 @@ def run_ours(args):
                     parity["one_call_rgb8_max_abs_vs_torchrun"] = d_rgb
                     parity["ok"] = bool(parity["ok"] and d_rgb == 0)     # same shards, same summation order: identical
                 multi.close()
+                torch.cuda.set_device(local_rank)
             except Exception as e:                      # e.g. the other GPUs are not visible to this rank
                 e2e_s = None
                 e2e_call = f"rtb200_multi_render unavailable here ({e}); e2e = the torchrun path"
         dist.barrier(group=host_group)                  # the other ranks wait on the HOST (gloo): their GPUs stay idle meanwhile
         barrier()
         if world > 1:
-            t = torch.tensor([e2e_s if (rank == 0 and e2e_s) else 0.0], dtype=torch.float64, device="cuda")
+            t = torch.tensor([e2e_s if (rank == 0 and e2e_s) else 0.0], dtype=torch.float64, device=torch.device("cuda", local_rank))
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_s = float(t.item()) or e2e_tr_s
             if e2e_call is None:

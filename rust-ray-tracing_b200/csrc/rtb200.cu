@@ -983,6 +983,13 @@ namespace {
 
 void multi_noop_progress(void*, uint64_t, uint64_t, double) {}
 
+// The multi-device calls switch the calling thread's current CUDA device as they go; the caller gets its own device back.
+struct DeviceRestore {
+    int dev = -1;
+    DeviceRestore() { if (cudaGetDevice(&dev) != cudaSuccess) { dev = -1; cudaGetLastError(); } }
+    ~DeviceRestore() { if (dev >= 0) cudaSetDevice(dev); }
+};
+
 int multi_ensure_buffers(rtb200_multi* m, size_t n_pix, bool want_sum) {
     if (m->pixels < n_pix) {
         for (int g = 0; g < m->n; g++) {
@@ -1028,6 +1035,7 @@ extern "C" {
 
 int rtb200_multi_create(const int32_t* devices, int32_t n_devices, rtb200_multi** out) {
     if (!out) return fail(RTB200_ERR_INVALID, "out is null");
+    DeviceRestore restore_device;
     *out = nullptr;
     if (n_devices < 1 || n_devices > RTB200_MAX_PEERS) return fail(RTB200_ERR_INVALID, "n_devices must be 1.." + std::to_string(RTB200_MAX_PEERS));
     rtb200_multi* m = new rtb200_multi();
@@ -1064,6 +1072,7 @@ int rtb200_multi_create(const int32_t* devices, int32_t n_devices, rtb200_multi*
 
 void rtb200_multi_destroy(rtb200_multi* m) {
     if (!m) return;
+    DeviceRestore restore_device;
     for (int g = 0; g < m->n; g++) {
         if (!m->ctx[g]) continue;                      // a shard rtb200_multi_create never got to
         cudaSetDevice(m->device[g]);
@@ -1093,6 +1102,7 @@ int rtb200_multi_info(rtb200_multi* m, int32_t* n_shards, int32_t* peer_access) 
 
 int rtb200_multi_upload_scene(rtb200_multi* m, const rtb200_scene* scene) {
     if (!m || !scene) return fail(RTB200_ERR_INVALID, "null argument");
+    DeviceRestore restore_device;
     for (int g = 0; g < m->n; g++) {
         int rc = rtb200_upload_scene(m->ctx[g], scene);
         if (rc) return rc;
@@ -1111,6 +1121,7 @@ int rtb200_multi_set_hit_mode(rtb200_multi* m, int32_t mode) {
 
 int rtb200_multi_set_progress(rtb200_multi* m, rtb200_progress_fn fn, void* user, int32_t interval_ms) {
     if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    DeviceRestore restore_device;
     if (interval_ms < 1) interval_ms = 1;
     for (int g = 0; g < m->n; g++) {   // the shards' kernels publish their queue heads; the polling is done by rtb200_multi_render
         int rc = rtb200_set_progress(m->ctx[g], fn ? multi_noop_progress : nullptr, nullptr, interval_ms);
@@ -1123,6 +1134,7 @@ int rtb200_multi_set_progress(rtb200_multi* m, rtb200_progress_fn fn, void* user
 int rtb200_multi_render(rtb200_multi* m, const rtb200_camera* camera, const rtb200_params* params, int32_t row_groups, uint8_t* rgb8_out,
                         float* linear_rgba_out, rtb200_stats* stats) {
     if (!m) return fail(RTB200_ERR_INVALID, "null argument");
+    DeviceRestore restore_device;
     int rc = validate_params(m->ctx[0], camera, params);
     if (rc) return rc;
     const int N = m->n;
