@@ -106,7 +106,9 @@ __device__ __forceinline__ void test_candidate(const ExactRay64& r, bool both_ro
             root1 = __dmul_rn(__dadd_rn(-hb, sq), r.inv_a);                                        // :271
             valid = (root1 >= T_MIN_D) && (root1 < INF_D);
         }
-        if (valid && root1 <= best_t) { best_t = root1; best_i = index; }                          // :141 (`<=`: last wins, F5)
+        // :141 — `t <= best` applied in list order keeps, among the hits of smallest t, the LAST object (F5).  Stated as an
+        // order-free rule (smaller t, or equal t and larger index) the candidates may be visited in any order.
+        if (valid && (root1 < best_t || (root1 == best_t && index > best_i))) { best_t = root1; best_i = index; }
     }
 }
 __device__ __forceinline__ double4 load_exact(const double4* __restrict__ p) {                     // 32 bytes, one sector
@@ -130,6 +132,8 @@ struct SmemSpheres {
 struct RegisterRays {
     const ExactRay* ray;
     __device__ __forceinline__ ExactRay load(int r) const { return ray[r]; }
+    __device__ __forceinline__ f3 origin(int r) const { return mk3(ray[r].ox, ray[r].oy, ray[r].oz); }
+    __device__ __forceinline__ bool both_roots() const { return ray[0].both_roots; }
 };
 
 // Drains one ray's deferred candidate list in sweep order.  list entry = {sign mask of up to 32 filter values (bit
@@ -347,42 +351,59 @@ struct Best { double t; int i; };                          // the running closes
 #define RTB_REFINE_INLINE __forceinline__   // two inlined copies (one per ray of the lane) beat one out-of-line copy by 5 %
 #endif
 
-// Next stage-1 candidate of the walk, in sweep order (false: none left).  The block index comes from the per-lane bitmap.
-__device__ __forceinline__ bool walk_next(const uint32_t* masks_r, int stride, uint32_t& todo, uint32_t& cand, int& last, int first_sphere,
-                                          int& idx) {
+// Next stage-1 candidate of the walk.  maddr = shared-memory byte address of the ray's mask word of the
+// chunk's block 0 (block b's word lies stride_bytes * b further); todo = bitmap of the blocks that hold candidates; the
+// block index comes from that per-lane bitmap, highest block first (the visiting order is free: test_candidate's update
+// rule does not depend on it).  base31 = index of sphere 31 of block 0.
+__device__ __forceinline__ void walk_next(uint32_t maddr, uint32_t stride_bytes, uint32_t& todo, uint32_t& cand, int& last, int base31, int& idx) {
+    uint32_t hi, bit;                                      // precondition: (cand | todo) != 0
     if (cand == 0u) {
-        if (todo == 0u) return false;
-        const int b = __ffs(todo) - 1;
-        todo &= todo - 1u;
-        cand = ~masks_r[b * stride];                       // not empty: stage 1 set the block's bit
-        last = first_sphere + b * SWEEP_BLOCK + (SWEEP_BLOCK - 1);
+        uint32_t w;
+        asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(todo));   // FLO / BMSK: one instruction each
+        asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
+        todo ^= bit;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(maddr + hi * stride_bytes));
+        cand = ~w;                                         // not empty: stage 1 set the block's bit
+        last = base31 + (int)(hi * SWEEP_BLOCK);
     }
-    uint32_t hi, bit;                                      // sphere j of the block sits at bit 31 - j: highest bit first
-    asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));       // FLO / BMSK: ptxas otherwise rebuilds clz and 0x80000000 >> clz
+    asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));       // sphere j of the block sits at bit 31 - j
     asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
     cand ^= bit;
     idx = last - (int)hi;
-    return true;
 }
 
+template <class RaySrc>
 __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
                                           const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, float h_bound, FilterRay f,
-                                          ExactRay ray32, Best best) {
+                                          const RaySrc& rays, int r, Best best) {
     if (todo == 0u) return best;
-    const ExactRay64 ray = promote_ray(ray32);
     // Near-root mode: a sphere whose centre lies behind the origin along the ray (half_b > 0) cannot give a valid root
     // (test_candidate).  The filter's own h = (c - o).D is that projection in FP32, off by at most 8u(|o| + |c| + r)
     // (rt_filter.h), so h < -16u(|o|_1 + max(|c| + r)) proves half_b > 0 and the f64 test is skipped: for a bounce ray
     // in the middle of the scene that is half of the stage-2 survivors.
-    const float h_min = ray32.both_roots ? -RTB_INF : -__fmul_rn(9.5367431640625e-07f, __fadd_rn(__fadd_rn(fabsf(ray32.ox), fabsf(ray32.oy)), __fadd_rn(fabsf(ray32.oz), h_bound)));
+    const bool both_roots = rays.both_roots();
+    float h_min = -RTB_INF;
+    if (!both_roots) {
+        const f3 o = rays.origin(r);
+        h_min = -__fmul_rn(9.5367431640625e-07f, __fadd_rn(__fadd_rn(fabsf(o.x), fabsf(o.y)), __fadd_rn(fabsf(o.z), h_bound)));
+    }
     uint32_t cand = 0;
     int last = 0, idx = 0;                                 // last = index of the current block's sphere 31
-    while (walk_next(masks_r, stride, todo, cand, last, first_sphere, idx)) {
+    // the mask words' shared-memory address, held in ONE register for the whole walk (left to itself ptxas rebuilds it from
+    // %tid and the shared window base on every block: five instructions per refill)
+    uint32_t maddr = (uint32_t)__cvta_generic_to_shared(masks_r);
+    asm volatile("" : "+r"(maddr));
+    while ((cand | todo) != 0u) {                          // one exit, at the top: no break out of the refill branch
+        walk_next(maddr, (uint32_t)stride * 4u, todo, cand, last, first_sphere + (SWEEP_BLOCK - 1), idx);
         const float4 fs = __ldg(&g_filter[idx]);
         float h;
         const float q = filter_value_h(f, fs.x, fs.y, fs.z, fs.w, h);                              // stage 2 (FP32, conservative)
-        if (!(__float_as_uint(q) >> 31) && !(h < h_min))
-            test_candidate(ray, ray32.both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);   // stage 3 (f64, exact)
+        if (!(__float_as_uint(q) >> 31) && !(h < h_min)) {
+            // stage 3 (f64, exact), ~0.3 times per ray and chunk: the ray is fetched and promoted HERE, so that nothing of it
+            // is live across the walk (the kernels run at the 64-register limit)
+            const ExactRay64 ray = promote_ray(rays.load(r));
+            test_candidate(ray, both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);
+        }
     }
     return best;
 }
@@ -456,7 +477,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -521,7 +542,7 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays.load(r), bst);
+            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
@@ -1093,10 +1114,14 @@ constexpr int SLOT_WORDS = 17;   // o 0-2, d 3-5, thr 6-8, acc 9-11, item 12, s 
 template <int RAYS, int THREADS>
 struct SmemRays {
     const uint32_t* st;
-    bool both_roots;
+    bool both;
+    __device__ __forceinline__ bool both_roots() const { return both; }
+    __device__ __forceinline__ f3 origin(int r) const {
+        return mk3(__uint_as_float(st[(0 * RAYS + r) * THREADS]), __uint_as_float(st[(1 * RAYS + r) * THREADS]), __uint_as_float(st[(2 * RAYS + r) * THREADS]));
+    }
     __device__ __forceinline__ ExactRay load(int r) const {
         ExactRay e;
-        e.both_roots = both_roots;
+        e.both_roots = both;
         e.ox = __uint_as_float(st[(0 * RAYS + r) * THREADS]); e.oy = __uint_as_float(st[(1 * RAYS + r) * THREADS]);
         e.oz = __uint_as_float(st[(2 * RAYS + r) * THREADS]); e.dx = __uint_as_float(st[(3 * RAYS + r) * THREADS]);
         e.dy = __uint_as_float(st[(4 * RAYS + r) * THREADS]); e.dz = __uint_as_float(st[(5 * RAYS + r) * THREADS]);
