@@ -476,8 +476,22 @@ int rtb200_camera_init(rtb200_camera* out, int32_t image_width, int32_t image_he
     return RTB200_OK;
 }
 
-int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
-    if (!ctx || !scene) return fail(RTB200_ERR_INVALID, "null argument");
+// The flattened scene as the device wants it, built ONCE on the host (rtb200_multi_upload_scene sends the same arena to every
+// device): arena = [exact f64 | spheres | filter | materials | stage-1 triples | kinds], each padded to whole 32-sphere blocks.
+struct HostScene {
+    int n = 0;
+    size_t cnt = 32;
+    std::vector<unsigned char> arena;
+    size_t off_sph = 0, off_flt = 0, off_mat = 0, off_slab = 0, off_kind = 0;
+    std::vector<float4> filter;                        // n entries (kernel-parameter variant of the one-stage sweep)
+    std::vector<float> slab;                           // cnt * 3 (kernel-parameter variant of the two-stage sweep)
+    int up_axis = 1, largest = 0;
+    float rp_min = 1.0f, h_bound = 0.0f;
+    double slab_pass = 1.0;
+};
+
+static int build_host_scene(const rtb200_scene* scene, HostScene& hs) {
+    if (!scene) return fail(RTB200_ERR_INVALID, "null argument");
     if (scene->n_spheres < 0 || scene->n_materials < 0) return fail(RTB200_ERR_INVALID, "negative count");
     if (scene->n_spheres > 0 && (!scene->spheres || !scene->materials)) return fail(RTB200_ERR_INVALID, "null scene arrays");
     const int n = scene->n_spheres;
@@ -515,18 +529,20 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
             std::vector<float> v((size_t)n);
             for (int ax = 0; ax < 3; ax++) {
                 for (int i = 0; i < n; i++) v[i] = ax == 0 ? sph[i].x : ax == 1 ? sph[i].y : sph[i].z;
-                std::sort(v.begin(), v.end());
-                spread[ax] = (double)v[(size_t)((n - 1) * 0.9)] - (double)v[(size_t)((n - 1) * 0.1)];
+                const size_t lo = (size_t)((n - 1) * 0.1), hi = (size_t)((n - 1) * 0.9);
+                std::nth_element(v.begin(), v.begin() + hi, v.end());
+                const float vhi = v[hi];
+                std::nth_element(v.begin(), v.begin() + lo, v.begin() + hi + 1);
+                spread[ax] = (double)vhi - (double)v[lo];
             }
             up = spread[0] <= spread[1] && spread[0] <= spread[2] ? 0 : (spread[1] <= spread[2] ? 1 : 2);
         }
         const int ia = (up + 1) % 3, ib = (up + 2) % 3;
-        const int padded = (int)cnt;
-        ctx->h_slab.assign((size_t)padded * 3, 0.0f);
+        hs.slab.assign(cnt * 3, 0.0f);
         const double extent = std::max(1e-30, 0.5 * (spread[ia] + spread[ib]));
-        for (int i = 0; i < padded; i++) {
-            float* o3 = &ctx->h_slab[(size_t)i * 3];
-            if (i < n) {
+        for (size_t i = 0; i < cnt; i++) {
+            float* o3 = &hs.slab[i * 3];
+            if ((int)i < n) {
                 const float c[3] = {sph[i].x, sph[i].y, sph[i].z};
                 o3[0] = c[ia]; o3[1] = c[ib];
                 o3[2] = rtb::slab_sphere_r(sph[i].x, sph[i].y, sph[i].z, sph[i].w);
@@ -534,20 +550,42 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
                 o3[2] = -INFINITY;                        // padding: never a candidate
             }
         }
-        ctx->slab_rp_min = rtb::slab_apply_floor(ctx->h_slab.data() + 2, n, 3);
+        hs.rp_min = rtb::slab_apply_floor(hs.slab.data() + 2, n, 3);
         // expected pass rate of stage 1: disc diameter over the scene's extent, inflated as for a ray that starts one
         // extent away from the origin (the 1 + M_r/R_min of make_slab_ray)
-        const double inflate = 1.0 + (double)RTB_FILTER_MARGIN * extent * extent / (double)ctx->slab_rp_min;
+        const double inflate = 1.0 + (double)RTB_FILTER_MARGIN * extent * extent / (double)hs.rp_min;
         double pass = 0.0;
-        for (int i = 0; i < n; i++) pass += std::min(1.0, 2.0 * std::sqrt((double)ctx->h_slab[(size_t)i * 3 + 2] * inflate) / extent);
-        ctx->up_axis = up;
-        ctx->slab_pass = n > 0 ? pass / n : 1.0;
+        for (int i = 0; i < n; i++) pass += std::min(1.0, 2.0 * std::sqrt((double)hs.slab[(size_t)i * 3 + 2] * inflate) / extent);
+        hs.up_axis = up;
+        hs.slab_pass = n > 0 ? pass / n : 1.0;
     }
+    hs.n = n; hs.cnt = cnt;
+    hs.off_sph = cnt * sizeof(double4); hs.off_flt = hs.off_sph + cnt * sizeof(float4); hs.off_mat = hs.off_flt + cnt * sizeof(float4);
+    hs.off_slab = hs.off_mat + cnt * sizeof(float4); hs.off_kind = hs.off_slab + cnt * 3 * sizeof(float);
+    hs.arena.resize(hs.off_kind + cnt * sizeof(int));      // cnt is a multiple of 32, so every array starts 32-byte aligned
+    std::memcpy(hs.arena.data(), ex.data(), cnt * sizeof(double4));
+    std::memcpy(hs.arena.data() + hs.off_sph, sph.data(), cnt * sizeof(float4));
+    std::memcpy(hs.arena.data() + hs.off_flt, flt.data(), cnt * sizeof(float4));
+    std::memcpy(hs.arena.data() + hs.off_mat, mat.data(), cnt * sizeof(float4));
+    std::memcpy(hs.arena.data() + hs.off_slab, hs.slab.data(), cnt * 3 * sizeof(float));
+    std::memcpy(hs.arena.data() + hs.off_kind, kind.data(), cnt * sizeof(int));
+    hs.filter.assign(flt.begin(), flt.begin() + n);
+    hs.largest = 0;
+    double hb = 0.0;
+    for (int i = 0; i < n; i++) {
+        hb = std::max(hb, std::sqrt((double)sph[i].x * sph[i].x + (double)sph[i].y * sph[i].y + (double)sph[i].z * sph[i].z) + std::fabs(scene->spheres[i].radius));
+        if (sph[i].w > sph[hs.largest].w) hs.largest = i;
+    }
+    hs.h_bound = std::nextafterf((float)(hb * (1.0 + 1e-6)), INFINITY);
+    return RTB200_OK;
+}
+
+// Sends the arena to ctx's device on `st` (one copy, reusing the device arena while it is large enough) and points the
+// context at it.  The copy is asynchronous when the caller says so (the source is pageable memory that must stay alive until
+// the stream has been synchronised: rtb200_multi_upload_scene overlaps the copies to all devices that way).
+static int commit_host_scene(rtb200_ctx* ctx, const HostScene& hs, cudaStream_t st, bool sync) {
     CU_TRY(cudaSetDevice(ctx->device));
-    // One device arena [exact f64 | spheres | filter | materials | stage-1 triples | kinds], reused while it is large enough,
-    // filled by ONE copy (cnt is a multiple of 32, so every array starts 32-byte aligned).
-    const size_t off_sph = cnt * sizeof(double4), off_flt = off_sph + cnt * sizeof(float4), off_mat = off_flt + cnt * sizeof(float4),
-                 off_slab = off_mat + cnt * sizeof(float4), off_kind = off_slab + cnt * 3 * sizeof(float), bytes = off_kind + cnt * sizeof(int);
+    const size_t bytes = hs.arena.size();
     if (ctx->scene_capacity < bytes) {
         cudaFree(ctx->d_scene);
         ctx->d_scene = nullptr; ctx->scene_capacity = 0;
@@ -555,32 +593,30 @@ int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
         CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
         ctx->scene_capacity = bytes;
     }
-    std::vector<unsigned char> host(bytes);
-    std::memcpy(host.data(), ex.data(), cnt * sizeof(double4));
-    std::memcpy(host.data() + off_sph, sph.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + off_flt, flt.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + off_mat, mat.data(), cnt * sizeof(float4));
-    std::memcpy(host.data() + off_slab, ctx->h_slab.data(), cnt * 3 * sizeof(float));
-    std::memcpy(host.data() + off_kind, kind.data(), cnt * sizeof(int));
-    CU_TRY(cudaMemcpy(ctx->d_scene, host.data(), bytes, cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpyAsync(ctx->d_scene, hs.arena.data(), bytes, cudaMemcpyHostToDevice, st));
+    if (sync) CU_TRY(cudaStreamSynchronize(st));
     unsigned char* base = static_cast<unsigned char*>(ctx->d_scene);
     ctx->d_exact = reinterpret_cast<double4*>(base);
-    ctx->d_spheres = reinterpret_cast<float4*>(base + off_sph);
-    ctx->d_filter = reinterpret_cast<float4*>(base + off_flt);
-    ctx->d_mat = reinterpret_cast<float4*>(base + off_mat);
-    ctx->d_slab = reinterpret_cast<float4*>(base + off_slab);
-    ctx->d_mat_kind = reinterpret_cast<int*>(base + off_kind);
-    ctx->n_padded = (int)cnt;
-    ctx->largest_sphere = 0;
-    {
-        double hb = 0.0;
-        for (int i = 0; i < n; i++) hb = std::max(hb, std::sqrt((double)sph[i].x * sph[i].x + (double)sph[i].y * sph[i].y + (double)sph[i].z * sph[i].z) + std::fabs(scene->spheres[i].radius));
-        ctx->h_bound = std::nextafterf((float)(hb * (1.0 + 1e-6)), INFINITY);
-    }
-    for (int i = 1; i < n; i++) if (sph[i].w > sph[ctx->largest_sphere].w) ctx->largest_sphere = i;
-    ctx->n_spheres = n;
-    ctx->h_filter.assign(flt.begin(), flt.begin() + n);
+    ctx->d_spheres = reinterpret_cast<float4*>(base + hs.off_sph);
+    ctx->d_filter = reinterpret_cast<float4*>(base + hs.off_flt);
+    ctx->d_mat = reinterpret_cast<float4*>(base + hs.off_mat);
+    ctx->d_slab = reinterpret_cast<float4*>(base + hs.off_slab);
+    ctx->d_mat_kind = reinterpret_cast<int*>(base + hs.off_kind);
+    ctx->n_padded = (int)hs.cnt;
+    ctx->n_spheres = hs.n;
+    ctx->h_filter = hs.filter;
+    ctx->h_slab = hs.slab;
+    ctx->up_axis = hs.up_axis; ctx->slab_rp_min = hs.rp_min; ctx->slab_pass = hs.slab_pass;
+    ctx->largest_sphere = hs.largest; ctx->h_bound = hs.h_bound;
     return RTB200_OK;
+}
+
+int rtb200_upload_scene(rtb200_ctx* ctx, const rtb200_scene* scene) {
+    if (!ctx || !scene) return fail(RTB200_ERR_INVALID, "null argument");
+    HostScene hs;
+    int rc = build_host_scene(scene, hs);
+    if (rc) return rc;
+    return commit_host_scene(ctx, hs, 0, true);
 }
 
 int rtb200_trace_device(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev, void* stream) {
@@ -1103,9 +1139,16 @@ int rtb200_multi_info(rtb200_multi* m, int32_t* n_shards, int32_t* peer_access) 
 int rtb200_multi_upload_scene(rtb200_multi* m, const rtb200_scene* scene) {
     if (!m || !scene) return fail(RTB200_ERR_INVALID, "null argument");
     DeviceRestore restore_device;
+    HostScene hs;                                      // flattened once; the same arena goes to every device, copies overlapped
+    int rc = build_host_scene(scene, hs);
+    if (rc) return rc;
     for (int g = 0; g < m->n; g++) {
-        int rc = rtb200_upload_scene(m->ctx[g], scene);
+        rc = commit_host_scene(m->ctx[g], hs, m->stream[g], false);
         if (rc) return rc;
+    }
+    for (int g = 0; g < m->n; g++) {
+        CU_TRY(cudaSetDevice(m->device[g]));
+        CU_TRY(cudaStreamSynchronize(m->stream[g]));
     }
     return RTB200_OK;
 }
