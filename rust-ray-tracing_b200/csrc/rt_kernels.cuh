@@ -131,7 +131,12 @@ struct SmemSpheres {
 // Where the drain reads a lane's rays from: registers (resident kernel) or the lane's path state in shared memory.
 struct RegisterRays {
     const ExactRay* ray;
-    __device__ __forceinline__ ExactRay load(int r) const { return ray[r]; }
+    // r may be a run-time value (drain_pending): select, never index (an indexed register array would go to local memory)
+    __device__ __forceinline__ ExactRay load(int r) const {
+        ExactRay e = ray[0];
+        if (r) { const ExactRay& o = ray[1]; e.ox = o.ox; e.oy = o.oy; e.oz = o.oz; e.dx = o.dx; e.dy = o.dy; e.dz = o.dz; e.inv_a = o.inv_a; }
+        return e;
+    }
     __device__ __forceinline__ f3 origin(int r) const { return mk3(ray[r].ox, ray[r].oy, ray[r].oz); }
     __device__ __forceinline__ bool both_roots() const { return ray[0].both_roots; }
 };
@@ -372,18 +377,34 @@ __device__ __forceinline__ void walk_next(uint32_t maddr, uint32_t stride_bytes,
     idx = last - (int)hi;
 }
 
-template <class RaySrc>
-__device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
+// Stage-2 survivors are not tested on the spot: a lane parks them in ONE register and the warp runs stage 3 once per
+// chunk for the survivors of all its rays together (drain_pending).  On the spot, stage 3 ran with ~6 of 32 lanes active,
+// 1.5 times per ray and chunk; deferred, the same lane-tests take ~1.7 passes per chunk for both rays.  The order is free
+// (test_candidate's rule).  pend = a stack of 9-bit entries (ray << 8 | sphere index within the chunk) above a sentinel 1:
+// empty = 1, three entries fill it; a fourth survivor of one lane in one chunk (rare) is tested on the spot — inline in the
+// parameter-space kernels (with a CALL inside the chunk loop ptxas moves the loop's counters and the stage-1 sphere operands
+// out of the uniform datapath, LDC into vector registers instead of LDCU, and the sweep drops to 74 % issue-slot use: C2
+// 54.9 ms), out of line in the kernels that read stage 1 from shared memory (no uniform operands to lose, and the walk
+// loop stays small: C4 460 vs 472 ms inline, 785 spheres 12.04 vs 12.37 ms).
+constexpr uint32_t PEND_EMPTY = 1u, PEND_FULL = 1u << 27;
+
+__device__ __noinline__ Best stage3_now(ExactRay ray32, double4 sphere, int idx, Best best) {
+    test_candidate(promote_ray(ray32), ray32.both_roots, sphere, idx, best.t, best.i);
+    return best;
+}
+
+// Stage 2 of the two-stage sweep for ray r and one chunk: the lane-parallel walk over its stage-1 candidates.
+template <bool CALL_OVERFLOW, class RaySrc>
+__device__ RTB_REFINE_INLINE void refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
                                           const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, float h_bound, FilterRay f,
-                                          const RaySrc& rays, int r, Best best) {
-    if (todo == 0u) return best;
+                                          const RaySrc& rays, int r, uint32_t& pend, Best& best) {
+    if (todo == 0u) return;
     // Near-root mode: a sphere whose centre lies behind the origin along the ray (half_b > 0) cannot give a valid root
     // (test_candidate).  The filter's own h = (c - o).D is that projection in FP32, off by at most 8u(|o| + |c| + r)
     // (rt_filter.h), so h < -16u(|o|_1 + max(|c| + r)) proves half_b > 0 and the f64 test is skipped: for a bounce ray
     // in the middle of the scene that is half of the stage-2 survivors.
-    const bool both_roots = rays.both_roots();
     float h_min = -RTB_INF;
-    if (!both_roots) {
+    if (!rays.both_roots()) {
         const f3 o = rays.origin(r);
         h_min = -__fmul_rn(9.5367431640625e-07f, __fadd_rn(__fadd_rn(fabsf(o.x), fabsf(o.y)), __fadd_rn(fabsf(o.z), h_bound)));
     }
@@ -399,19 +420,38 @@ __device__ RTB_REFINE_INLINE Best refine_chunk(const uint32_t* masks_r, int stri
         float h;
         const float q = filter_value_h(f, fs.x, fs.y, fs.z, fs.w, h);                              // stage 2 (FP32, conservative)
         if (!(__float_as_uint(q) >> 31) && !(h < h_min)) {
-            // stage 3 (f64, exact), ~0.3 times per ray and chunk: the ray is fetched and promoted HERE, so that nothing of it
-            // is live across the walk (the kernels run at the 64-register limit)
-            const ExactRay64 ray = promote_ray(rays.load(r));
-            test_candidate(ray, both_roots, load_exact(&g_exact[idx]), idx, best.t, best.i);
+            if (pend < PEND_FULL) pend = (pend << 9) | (uint32_t)(idx - first_sphere + (r << 8));  // park it for drain_pending
+            else if (CALL_OVERFLOW) best = stage3_now(rays.load(r), load_exact(&g_exact[idx]), idx, best);   // the lane's fourth: now
+            else test_candidate(promote_ray(rays.load(r)), rays.both_roots(), load_exact(&g_exact[idx]), idx, best.t, best.i);
         }
     }
-    return best;
+}
+
+// Stage 3 (f64, exact) for the parked survivors of all RAYS rays of the lane: one pass per entry of the fullest lane.  The
+// ray is fetched and promoted HERE, so that nothing of it is live across the walks (the kernels run at the 64-register limit).
+template <int RAYS, class RaySrc>
+__device__ __forceinline__ void drain_pending(uint32_t pend, int first_sphere, const double4* __restrict__ g_exact, const RaySrc& rays,
+                                              double (&best_t)[RAYS], int (&best_i)[RAYS]) {
+    static_assert(RAYS <= 2, "a pending entry has one ray bit");
+    while (pend != PEND_EMPTY) {
+        const uint32_t e = pend & 511u;
+        pend >>= 9;
+        const int r = (int)(e >> 8), idx = first_sphere + (int)(e & 255u);
+        const ExactRay ray32 = rays.load(r);
+        double bt = best_t[0];
+        int bi = best_i[0];
+        if (RAYS > 1 && r) { bt = best_t[RAYS - 1]; bi = best_i[RAYS - 1]; }
+        test_candidate(promote_ray(ray32), ray32.both_roots, load_exact(&g_exact[idx]), idx, bt, bi);
+        if (RAYS > 1 && r) { best_t[RAYS - 1] = bt; best_i[RAYS - 1] = bi; }
+        else { best_t[0] = bt; best_i[0] = bi; }
+    }
 }
 
 // Stage-1 operand sources: evaluate the slab test of one 32-sphere block for the RAYS rays of a lane.
 // ParamSlab: {c_a, c_b, R'} triples in kernel parameter space -> LDCU.64 x3 per sphere pair, uniform-register operands.
 template <class PV_T>
 struct ParamSlab {
+    static constexpr bool overflow_by_call = false;   // refine_chunk: keep the chunk loop free of calls (uniform datapath)
     const PV_T& pv;
     template <int RAYS>
     __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
@@ -430,6 +470,7 @@ struct ParamSlab {
 // SmemSlab: the same triples staged in shared memory (scenes too large for parameter space): three LDS.128 broadcasts
 // per four spheres, each serving the RAYS rays of the lane.
 struct SmemSlab {
+    static constexpr bool overflow_by_call = true;
     const float4* s;
     template <int RAYS>
     __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
@@ -474,13 +515,15 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
             }
         }
         // ---- stages 2 and 3 ----
+        uint32_t pend = PEND_EMPTY;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, bst);
+            refine_chunk<S1::overflow_by_call>(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
+        drain_pending<RAYS>(pend, cb * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
     }
 }
 
@@ -539,13 +582,15 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
             }
         }
         __syncwarp();                                         // all lanes are done reading this half before chunk c + 2 refills it
+        uint32_t pend = PEND_EMPTY;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
             Best bst{best_t[r], best_i[r]};
-            bst = refine_chunk(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, bst);
+            refine_chunk<true>(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
+        drain_pending<RAYS>(pend, c * 8 * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
     }
     cp_async_wait<0>();
 }

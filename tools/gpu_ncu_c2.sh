@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu of the default bench command's trace kernel (C2): launch list, then one --set full capture
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --workload C2 --steps 1 --warmup 3 --no-cpu-baseline --no-parity"
 $CMD > gpurun_out/plain_c2.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/plain_c2.log; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches_c2.csv $CMD > gpurun_out/ncu_c2a.log 2>&1
 grep -c k_trace_paths gpurun_out/launches_c2.csv
