@@ -190,6 +190,27 @@ int rtb200_intersect_batch_f64(rtb200_ctx* ctx, const double* ox, const double* 
 int rtb200_trace_device(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev,
                         void* stream);
 
+/* rtb200_trace_device WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernels, same arguments, same result (bit-identical accum_dev) as rtb200_trace_device, but the trace step's scratch —
+ * the counters / work-queue head and the partial planes of the sample splits that k_combine sums into accum_dev — lives in
+ * ONE file-scope `static __device__` array of RTB200_STATIC_SCRATCH_BYTES (+ a 256-byte header) that every GPU which loads
+ * the library holds until the process exits.  The call makes no cudaMalloc / cudaFree / event creation: it clears the
+ * counter words (stream-ordered memset), launches the trace kernel and, when the sample range was split, k_combine.
+ *  - Limit: a shard whose partial planes (sample splits x traced pixels x 16 B) exceed RTB200_STATIC_SCRATCH_BYTES is
+ *    rejected with RTB200_ERR_INVALID and a message naming both sizes; trace fewer rows per call (row_begin / row_end).
+ *    The library picks the number of splits K <= 64 from the traced pixels and samples (more splits for fewer pixels), so a
+ *    call that traces <= 32 768 pixels always fits; C1 in one call (400x225x16 spp, K = 16) needs 23 MB.
+ *  - Every call on a GPU shares the array and it keeps the last call's contents; what must start at zero (the counters) is
+ *    cleared by the call itself.  Calls that overlap on the GPU (different streams, or several contexts on one device)
+ *    RACE on it: serialise them.  rtb200_read_counters / rtb200_trace_kernel_stats do not see these launches.
+ *  - The scene (rtb200_upload_scene) and accum_dev are set up beforehand by the caller; the first call on a device resolves
+ *    the array's device address (cudaGetSymbolAddress) and sets the kernels' shared-memory attribute.
+ * *scratch_bytes_used (may be null) = bytes of the array this call used. */
+#define RTB200_STATIC_SCRATCH_BYTES 33554432 /* 32 MiB */
+int rtb200_trace_device_static(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev,
+                               void* stream, uint64_t* scratch_bytes_used);
+
 /* Resolve kernel: sum/spp + Color::to_u8_array (src/renderer.rs:161-163, src/color.rs:54-64).
  * accum_dev: n_pixels float4; rgb8_dev: n_pixels*3 bytes (device).  Asynchronous. */
 int rtb200_resolve_device(rtb200_ctx* ctx, const void* accum_dev, int64_t n_pixels, int32_t samples_per_pixel,

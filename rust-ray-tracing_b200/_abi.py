@@ -11,7 +11,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtb200.so")
 
-from ._abi_types import (OK, ERR_INVALID, ERR_CUDA, ERR_STATE, LAMBERTIAN, METAL, DIELECTRIC, Material, Sphere, Scene, Camera, Params, Stats)  # noqa: F401
+from ._abi_types import (OK, ERR_INVALID, ERR_CUDA, ERR_STATE, LAMBERTIAN, METAL, DIELECTRIC, Material, Sphere, Scene, Camera, Params, Stats,
+                         STATIC_SCRATCH_BYTES)  # noqa: F401
 
 
 # every symbol include/rtb200.h declares: name -> (restype, argtypes)
@@ -31,6 +32,7 @@ SYMBOLS = {
     "rtb200_intersect_batch": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P]),
     "rtb200_intersect_batch_f64": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P]),
     "rtb200_trace_device": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P]),
+    "rtb200_trace_device_static": (C.c_int, [_P, C.POINTER(Camera), C.POINTER(Params), _P, _P, C.POINTER(C.c_uint64)]),
     "rtb200_resolve_device": (C.c_int, [_P, _P, C.c_int64, C.c_int32, _P, _P]),
     "rtb200_intersect_batch_device": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _P, C.c_int64, _P, _P, _P]),
     "rtb200_device_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),

@@ -6,6 +6,7 @@ import ctypes as C
 
 OK, ERR_INVALID, ERR_CUDA, ERR_STATE = 0, -1, -2, -3
 LAMBERTIAN, METAL, DIELECTRIC = 0, 1, 2
+STATIC_SCRATCH_BYTES = 33554432   # RTB200_STATIC_SCRATCH_BYTES: capacity of the static scratch of rtb200_trace_device_static
 
 
 class Material(C.Structure):

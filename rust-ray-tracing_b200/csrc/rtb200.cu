@@ -154,11 +154,21 @@ int choose_splits_log2(const rtb200_ctx* ctx, long long n_pix, int n_samples) {
     return lg;
 }
 
-int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p, float4* accum, cudaStream_t st) {
+// Scratch override of launch_trace (rtb200_trace_device_static): the counters / work-queue head and the partial planes live
+// in caller-named memory of fixed capacity instead of the context's growable buffers, and no event pair is recorded.
+struct TraceScratch {
+    unsigned long long* counters;   // 3 words: paths, segments, work-queue head
+    float4* partial;                // partial planes of the sample splits
+    size_t partial_elems;           // capacity in float4
+};
+
+int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params* p, float4* accum, cudaStream_t st,
+                 const TraceScratch* ext = nullptr) {
     const int W = cam->image_width;
+    unsigned long long* const d_counters = ext ? ext->counters : ctx->d_counters;
     const int row_stride = p->row_stride > 1 ? p->row_stride : 1;
     const long long n_pix = (long long)((p->row_end - p->row_begin + row_stride - 1) / row_stride) * W;   // traced rows x W
-    CU_TRY(cudaMemsetAsync(ctx->d_counters, 0, 3 * sizeof(unsigned long long), st));
+    CU_TRY(cudaMemsetAsync(d_counters, 0, 3 * sizeof(unsigned long long), st));
     if (n_pix == 0) return RTB200_OK;
     const int n_samples = p->sample_end - p->sample_begin;
     rtb::TraceParams P;
@@ -183,11 +193,20 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         if (const char* e = std::getenv("RTB200_CLAIM_CHUNK")) { int v = std::atoi(e); if (v >= 1 && v <= 4096) chunk = v; }
         P.claim_chunk = chunk;
     }
-    P.work_counter = ctx->d_counters + 2;
+    P.work_counter = d_counters + 2;
     P.progress = (ctx->progress_cb && ctx->h_progress) ? ctx->d_progress : nullptr;
     if (ctx->h_progress) *ctx->h_progress = 0ull;
-    P.counters = ctx->d_counters;
-    if (splits > 1) {
+    P.counters = d_counters;
+    float4* d_partial = nullptr;
+    if (splits > 1 && ext) {
+        const size_t want = (size_t)splits * (size_t)n_pix;
+        if (want > ext->partial_elems)
+            return fail(RTB200_ERR_INVALID, "rtb200_trace_device_static: this shard needs " + std::to_string(want * sizeof(float4)) +
+                        " bytes of partial planes (" + std::to_string(splits) + " sample splits x " + std::to_string(n_pix) +
+                        " pixels x 16 B), beyond the static scratch maximum of " + std::to_string(ext->partial_elems * sizeof(float4)) +
+                        " bytes: render fewer rows per call (row_begin/row_end) or use rtb200_trace_device");
+        P.out = d_partial = ext->partial;
+    } else if (splits > 1) {
         size_t want = (size_t)splits * (size_t)n_pix;
         if (ctx->partial_elems < want) {
             if (ctx->d_partial) cudaFree(ctx->d_partial);
@@ -195,7 +214,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
             CU_TRY(cudaMalloc(&ctx->d_partial, want * sizeof(float4)));
             ctx->partial_elems = want;
         }
-        P.out = ctx->d_partial;
+        P.out = d_partial = ctx->d_partial;
     } else {
         P.out = accum;
     }
@@ -285,8 +304,10 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         std::memcpy(ps->s1, ctx->h_slab.data(), ctx->h_slab.size() * sizeof(float));
     };
     cudaEvent_t* ring = ctx->ev_trace[ctx->trace_launches % rtb200_ctx::TRACE_RING];
-    if (!ring[0]) { CU_TRY(cudaEventCreate(&ring[0])); CU_TRY(cudaEventCreate(&ring[1])); }
-    CU_TRY(cudaEventRecord(ring[0], st));
+    if (!ext) {
+        if (!ring[0]) { CU_TRY(cudaEventCreate(&ring[0])); CU_TRY(cudaEventCreate(&ring[1])); }
+        CU_TRY(cudaEventRecord(ring[0], st));
+    }
     ctx->last_splits = splits;
     if (streamed) {
         ctx->last_kernel = "k_trace_paths_g<640,2> (two-stage, stage-1 triples streamed per warp from global memory)";
@@ -336,12 +357,14 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         launch_streamed();                                 // nothing else holds the scene
     }
     CU_TRY(cudaGetLastError());
-    CU_TRY(cudaEventRecord(ring[1], st));
-    ctx->trace_launches++;
+    if (!ext) {
+        CU_TRY(cudaEventRecord(ring[1], st));
+        ctx->trace_launches++;
+    }
     ctx->launches++;
     if (splits > 1) {
         int blocks = (int)((n_pix + 255) / 256);
-        rtb::k_combine<<<blocks, 256, 0, st>>>(ctx->d_partial, splits, n_pix, accum + (size_t)p->row_begin * W, W, (long long)(row_stride - 1) * W);
+        rtb::k_combine<<<blocks, 256, 0, st>>>(d_partial, splits, n_pix, accum + (size_t)p->row_begin * W, W, (long long)(row_stride - 1) * W);
         CU_TRY(cudaGetLastError());
         ctx->launches++;
     }
@@ -625,6 +648,56 @@ int rtb200_trace_device(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb2
     if (!accum_dev) return fail(RTB200_ERR_INVALID, "accum_dev is null");
     CU_TRY(cudaSetDevice(ctx->device));
     return launch_trace(ctx, camera, params, static_cast<float4*>(accum_dev), static_cast<cudaStream_t>(stream));
+}
+
+// ---- rtb200_trace_device_static: the trace step with its scratch in a file-scope device array (no allocation) -------------
+// Layout of the array: a 256-byte header (3 counter words: paths, segments, work-queue head) followed by the partial planes.
+// One array per GPU that loads this library, held until the process exits; every call on that GPU shares it.
+#define RTB200_STATIC_HEADER_BYTES 256
+static __device__ __align__(256) unsigned char g_static_scratch[RTB200_STATIC_HEADER_BYTES + RTB200_STATIC_SCRATCH_BYTES];
+
+namespace {
+// Device address of g_static_scratch per CUDA device.  In host code the NAME g_static_scratch is only a host-side stand-in
+// for the symbol (not a device address): it is resolved here once per device, with that device current, and only the
+// resolved pointer is handed to kernels and memsets.
+constexpr int MAX_DEVICES_STATIC = 64;
+unsigned char* g_static_scratch_dev[MAX_DEVICES_STATIC] = {};
+
+int static_scratch_for(int device, unsigned char** out) {
+    if (device < 0 || device >= MAX_DEVICES_STATIC) return fail(RTB200_ERR_INVALID, "device index beyond the static-scratch table");
+    if (!g_static_scratch_dev[device]) {
+        CU_TRY(cudaSetDevice(device));
+        void* p = nullptr;
+        CU_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail(RTB200_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+        g_static_scratch_dev[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_static_scratch_dev[device];
+    return RTB200_OK;
+}
+}  // namespace
+
+int rtb200_trace_device_static(rtb200_ctx* ctx, const rtb200_camera* camera, const rtb200_params* params, void* accum_dev, void* stream,
+                               uint64_t* scratch_bytes_used) {
+    int rc = validate_params(ctx, camera, params);
+    if (rc) return rc;
+    if (!accum_dev) return fail(RTB200_ERR_INVALID, "accum_dev is null");
+    CU_TRY(cudaSetDevice(ctx->device));
+    unsigned char* base = nullptr;
+    rc = static_scratch_for(ctx->device, &base);
+    if (rc) return rc;
+    TraceScratch sc;
+    sc.counters = reinterpret_cast<unsigned long long*>(base);
+    sc.partial = reinterpret_cast<float4*>(base + RTB200_STATIC_HEADER_BYTES);
+    sc.partial_elems = (size_t)RTB200_STATIC_SCRATCH_BYTES / sizeof(float4);
+    rc = launch_trace(ctx, camera, params, static_cast<float4*>(accum_dev), static_cast<cudaStream_t>(stream), &sc);
+    if (rc) return rc;
+    if (scratch_bytes_used) {
+        const int rs = params->row_stride > 1 ? params->row_stride : 1;
+        const uint64_t n_pix = (uint64_t)((params->row_end - params->row_begin + rs - 1) / rs) * (uint64_t)camera->image_width;
+        *scratch_bytes_used = RTB200_STATIC_HEADER_BYTES + (n_pix > 0 && ctx->last_splits > 1 ? n_pix * (uint64_t)ctx->last_splits * sizeof(float4) : 0);
+    }
+    return RTB200_OK;
 }
 
 int rtb200_resolve_device(rtb200_ctx* ctx, const void* accum_dev, int64_t n_pixels, int32_t samples_per_pixel, void* rgb8_dev, void* stream) {

@@ -220,6 +220,17 @@ class CudaRenderer(Renderer):
         p = self._params(max_bounces, samples_per_pixel, camera, sample_range, row_range)
         _abi.check(_abi.lib.rtb200_trace_device(self._ctx, C.byref(camera.abi), C.byref(p), C.c_void_p(accum_ptr), C.c_void_p(stream)))
 
+    def trace_device_static(self, max_bounces: int, samples_per_pixel: int, camera: Camera, accum_ptr: int, stream: int = 0,
+                            sample_range=None, row_range=None) -> int:
+        """rtb200_trace_device_static: the same trace step with its scratch in the library's file-scope device array — no
+        allocation inside the call.  Returns the bytes of the array the call used; raises Rtb200Error (ERR_INVALID) when
+        the shard's partial planes exceed RTB200_STATIC_SCRATCH_BYTES."""
+        p = self._params(max_bounces, samples_per_pixel, camera, sample_range, row_range)
+        used = C.c_uint64(0)
+        _abi.check(_abi.lib.rtb200_trace_device_static(self._ctx, C.byref(camera.abi), C.byref(p), C.c_void_p(accum_ptr), C.c_void_p(stream),
+                                                       C.byref(used)))
+        return int(used.value)
+
     def resolve_device(self, accum_ptr: int, n_pixels: int, samples_per_pixel: int, rgb8_ptr: int, stream: int = 0) -> None:
         _abi.check(_abi.lib.rtb200_resolve_device(self._ctx, C.c_void_p(accum_ptr), int(n_pixels), int(samples_per_pixel),
                                                   C.c_void_p(rgb8_ptr), C.c_void_p(stream)))
