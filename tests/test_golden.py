@@ -117,7 +117,8 @@ def test_cuda_render_matches_golden(rtb, renderer, name, stages):
     # and against the reference-faithful f64 oracle: the FP32 path state (hit points, normals, scattered directions) makes a
     # few silhouette samples take another branch, so this comparison is statistical
     d64 = np.abs(lin[..., :3].astype(np.float64) / spp - g["sum_f64"] / spp)
-    assert np.median(d64) < 1e-5 and (d64.max(axis=2) > 1e-4).mean() < 0.05
+    # (measured on the four fixtures: 0 / 0.26 % / 0.04 % / 0 of the pixels beyond 1e-4, median 8e-9; the all-FP32 sweep of round 1: < 5 %)
+    assert np.median(d64) < 1e-7 and (d64.max(axis=2) > 1e-4).mean() < 0.01
 
 
 @pytest.mark.gpu
