@@ -94,6 +94,8 @@ struct rtb200_ctx {
     bool attrs_set = false;
     bool intersect_attr_set = false;
     int default_rays = 0;                              // 0 = choose by scene size
+    std::vector<void*> exchange_allocs;                // buffers handed out by rtb200_device_alloc (rtb200_device_free accepts only these)
+    std::vector<void*> ipc_mappings;                   // peer buffers mapped by rtb200_ipc_open (rtb200_ipc_close accepts only these)
 };
 
 namespace {
@@ -439,6 +441,8 @@ int rtb200_create(int32_t device, rtb200_ctx** out) {
 void rtb200_destroy(rtb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    for (void* m : c->ipc_mappings) cudaIpcCloseMemHandle(m);     // what the caller left open
+    for (void* b : c->exchange_allocs) cudaFree(b);
     cudaFree(c->d_scene); cudaFree(c->d_counters);
     cudaFree(c->d_accum); cudaFree(c->d_rgb8); cudaFree(c->d_partial); cudaFree(c->d_rays); cudaFree(c->d_probe);
     for (int i = 0; i < 4; i++) if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -863,13 +867,18 @@ int rtb200_device_alloc(rtb200_ctx* ctx, size_t bytes, void** dev_out) {
     CU_TRY(cudaSetDevice(ctx->device));
     CU_TRY(cudaMalloc(dev_out, bytes > 0 ? bytes : 1));
     CU_TRY(cudaMemset(*dev_out, 0, bytes > 0 ? bytes : 1));
+    ctx->exchange_allocs.push_back(*dev_out);
     return RTB200_OK;
 }
 
 int rtb200_device_free(rtb200_ctx* ctx, void* dev) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    if (!dev) return RTB200_OK;
+    auto it = std::find(ctx->exchange_allocs.begin(), ctx->exchange_allocs.end(), dev);
+    if (it == ctx->exchange_allocs.end()) return fail(RTB200_ERR_INVALID, "rtb200_device_free: not a buffer of this context's rtb200_device_alloc");
     CU_TRY(cudaSetDevice(ctx->device));
     CU_TRY(cudaFree(dev));
+    ctx->exchange_allocs.erase(it);
     return RTB200_OK;
 }
 
@@ -890,13 +899,17 @@ int rtb200_ipc_open(rtb200_ctx* ctx, const uint8_t handle[RTB200_IPC_HANDLE_BYTE
     cudaIpcMemHandle_t h;
     std::memcpy(&h, handle, sizeof h);
     CU_TRY(cudaIpcOpenMemHandle(dev_out, h, cudaIpcMemLazyEnablePeerAccess));
+    ctx->ipc_mappings.push_back(*dev_out);
     return RTB200_OK;
 }
 
 int rtb200_ipc_close(rtb200_ctx* ctx, void* dev) {
     if (!ctx) return fail(RTB200_ERR_INVALID, "ctx is null");
+    auto it = std::find(ctx->ipc_mappings.begin(), ctx->ipc_mappings.end(), dev);
+    if (it == ctx->ipc_mappings.end()) return fail(RTB200_ERR_INVALID, "rtb200_ipc_close: not a mapping of this context's rtb200_ipc_open");
     CU_TRY(cudaSetDevice(ctx->device));
     CU_TRY(cudaIpcCloseMemHandle(dev));
+    ctx->ipc_mappings.erase(it);
     return RTB200_OK;
 }
 

@@ -284,6 +284,16 @@ def test_errors_are_reported_not_fatal(rtb, renderer):
         renderer.render(-1, 4, scene, cam)
     img, stat = renderer.render(5, 2, scene, cam)                # still usable afterwards
     assert img.shape == (9, 16, 3)
+    # exchange buffers: only what this context handed out can be freed / closed through it
+    buf = renderer.device_alloc(256)
+    with pytest.raises(rtb.Rtb200Error) as e:
+        renderer.device_free(buf + 64)
+    assert e.value.code == rtb._abi.ERR_INVALID
+    with pytest.raises(rtb.Rtb200Error):
+        renderer.ipc_close(buf)                                  # never opened with rtb200_ipc_open
+    renderer.device_free(buf)
+    with pytest.raises(rtb.Rtb200Error):
+        renderer.device_free(buf)                                # double free is an error, not a crash
 
 
 def test_fp32_peak_probe(renderer):
