@@ -1,4 +1,4 @@
-// vote_probe.cu — design-space probe for a TRANSPOSED stage 1 (diagnostic, not product code).
+// vote_probe.cu — design-space probes for stage 1 of the two-stage sweep (diagnostic, not product code).
 //   MODE 0: the product's LDS-fed form: rays per lane (RAYS = 2), sphere triples {c_a, c_b, R'} broadcast from shared memory
 //           (three LDS.128 per four spheres), 3 FFMA + SHF per pair.
 //   MODE 1: transposed: a lane holds K = 8 spheres {c_a, c_b, rho} of a 256-sphere chunk in registers (coalesced LDG.128 from
@@ -114,6 +114,54 @@ __global__ void __launch_bounds__(THREADS, MINB) k_lds_seq(const float4* __restr
                     for (int k = 0; k < 4 * GROUP; k++) m = __funnelshift_l(__float_as_uint(__fmaf_rn(-t[k], t[k], rp[k])), m, 1);
                 }
                 mask[r] = m;
+            }
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) acc += __popc(~mask[r]);
+        }
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) nou[r] = __fadd_rn(nou[r], 0.001f);
+    }
+    out[tid] = acc;
+}
+
+// MODE 3 ---------------------------------------------------------------------------------------------------------------
+// LDS-fed with PAIRED LANES: a lane sweeps 4 rays (its own two and its partner's, lane ^ 1) over HALF of the blocks (even
+// lanes the even blocks, odd lanes the odd ones): one LDS.128 group serves four rays, so only one FFMA in four meets a
+// sphere operand that is not in the operand-reuse cache.  Same pair-tests per lane as MODE 0.
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) k_lds_pair(const float4* __restrict__ g_s1, int n_spheres, const float* __restrict__ rays, int reps,
+                                                            unsigned* __restrict__ out) {
+    extern __shared__ float4 sm[];
+    for (int i = threadIdx.x; i < n_spheres * 3 / 4; i += THREADS) sm[i] = g_s1[i];
+    __syncthreads();
+    constexpr int RAYS = 4;
+    float ua[RAYS], ub[RAYS], nou[RAYS];
+    long long tid = (long long)blockIdx.x * THREADS + threadIdx.x;
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        const float* p = rays + (tid * 2 + r) * 6;
+        float il = rsqrtf(p[3] * p[3] + p[5] * p[5]);
+        ua[r] = p[5] * il; ub[r] = -p[3] * il;
+        nou[r] = -(p[0] * ua[r] + p[2] * ub[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+        ua[2 + r] = __shfl_xor_sync(0xffffffffu, ua[r], 1); ub[2 + r] = __shfl_xor_sync(0xffffffffu, ub[r], 1);
+        nou[2 + r] = __shfl_xor_sync(0xffffffffu, nou[r], 1);
+    }
+    unsigned acc = 0;
+    const int odd = threadIdx.x & 1;
+    for (int rep = 0; rep < reps; rep++) {
+#pragma unroll 1
+        for (int blk = 0; blk < n_spheres / 32; blk += 2) {
+            unsigned mask[RAYS];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = 0;
+            const float4* q = sm + (blk + odd) * 24;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const float4 A = q[3 * j], B = q[3 * j + 1], C = q[3 * j + 2];
+                SLAB(A.x, A.y, A.z) SLAB(A.w, B.x, B.y) SLAB(B.z, B.w, C.x) SLAB(C.y, C.z, C.w)
             }
 #pragma unroll
             for (int r = 0; r < RAYS; r++) acc += __popc(~mask[r]);
@@ -254,6 +302,8 @@ int main() {
         printf("-- %d spheres\n", ns);
         run("LDS-fed 2 rays/lane 640x1", k_lds<640, 1>, 640, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
         if (ns == 512) run("LDS-fed 2 rays/lane 256x4", k_lds<256, 4>, 256, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
+        run("LDS-fed paired lanes (4 rays, half blocks) 640x1", k_lds_pair<640, 1>, 640, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
+        run("LDS-fed paired lanes (4 rays, half blocks) 576x1", k_lds_pair<576, 1>, 576, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
         run("LDS-fed ray-sequential group 1 640x1", k_lds_seq<640, 1, 1>, 640, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
         run("LDS-fed ray-sequential group 2 640x1", k_lds_seq<640, 1, 2>, 640, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
         run("LDS-fed ray-sequential group 4 640x1", k_lds_seq<640, 1, 4>, 640, (size_t)ns * 12, nsm, d_s1, ns, d_rays, d_out, reps);
