@@ -1,0 +1,209 @@
+"""A SECOND, independently written restatement of the reference's hit routine, closest-hit update, finalize and the
+deterministic parts of the materials — in pure Python with exact fused multiply-adds (rational arithmetic, rounded once) —
+against the C++ oracle (oracle/rt_oracle.hpp, f64 instantiation), bit for bit.
+
+Why: the reference holds no tests or golden vectors and cannot be built here (no Rust), so the oracle is "parity unpinned"
+at the reference boundary.  What can be done is to rule out transcription slips: this file was written from
+the reference's source lines alone (cited per function, paths relative to the reference root), shares no code with the C++
+oracle, and must agree with it exactly — operation order, mul_add sites, the `<=` tie rule, near-root-only validity,
+front-face flip.  CPU only; small cases (pure-Python loops)."""
+import math
+from fractions import Fraction
+
+import numpy as np
+import pytest
+
+INF = float("inf")
+
+
+def fsqrt(x: float) -> float:
+    """f64::sqrt: NaN for a negative argument (math.sqrt raises instead)."""
+    return math.sqrt(x) if x >= 0.0 else float("nan")
+
+
+def fma(a: float, b: float, c: float) -> float:
+    """f64::mul_add: a*b + c rounded once (exact rational arithmetic; float() of a Fraction rounds to nearest even)."""
+    return float(Fraction(a) * Fraction(b) + Fraction(c))
+
+
+# ---- src/geometry.rs:434-468 (PackedVec3: the SIMD lanes use mul_add) ------------------------------------------------
+def p_dot(a, b):                       # :466-468  self.z.mul_add(rhs.z, self.y.mul_add(rhs.y, self.x * rhs.x))
+    return fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0]))
+
+
+def p_length_squared(a):               # :434-436
+    return fma(a[2], a[2], fma(a[1], a[1], a[0] * a[0]))
+
+
+# ---- src/geometry.rs:105-188 (scalar Vec3: plain multiplies and adds, no mul_add) --------------------------------------
+def s_dot(a, b):                       # :121-123
+    return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]
+
+
+def s_length_squared(a):               # :106-108  x.powi(2) + y.powi(2) + z.powi(2)
+    return a[0] * a[0] + a[1] * a[1] + a[2] * a[2]
+
+
+def s_reflect(v, n):                   # :179-181  self - 2.0 * self.dot(n) * n
+    k = 2.0 * s_dot(v, n)
+    return [v[i] - k * n[i] for i in range(3)]
+
+
+def s_refract(v, n, ratio):            # :183-188
+    cos_theta = min(s_dot([-x for x in v], n), 1.0)
+    perp = [ratio * (v[i] + cos_theta * n[i]) for i in range(3)]
+    par_k = -fsqrt(abs(1.0 - s_length_squared(perp)))
+    return [perp[i] + par_k * n[i] for i in range(3)]
+
+
+def reflectance(cosine, ior):          # src/materials.rs:121-124
+    r0 = ((1.0 - ior) / (1.0 + ior)) ** 2
+    one_minus = 1.0 - cosine
+    p5 = one_minus * one_minus * one_minus * one_minus * one_minus       # powi(5): repeated multiplication
+    return r0 + (1.0 - r0) * p5
+
+
+# ---- src/objects.rs:249-290 + :140-147: one ray against the object list ------------------------------------------------
+def sweep(spheres, o, d, enabled=True, t_min=0.001, t_max=INF):
+    """for object in objects { object.hit_packed(rays, &(0.001..INFINITY), &mut records) } for ONE lane
+    (src/ray_tracing.rs:397-403).  Returns (index or -1, t, un-normalised outward normal)."""
+    best_t, best_i, best_n = INF, -1, None                                  # PackedHitRecords::default, :121-134
+    for i, (cx, cy, cz, r) in enumerate(spheres):
+        oc = [o[0] - cx, o[1] - cy, o[2] - cz]                              # :252
+        a = p_length_squared(d)                                             # :253
+        inverse_a = 1.0 / a                                                 # :254
+        half_b = p_dot(oc, d)                                               # :255
+        c = p_length_squared(oc) - r * r                                    # :256  radius.powi(2)
+        disc = fma(half_b, half_b, -(a * c))                                # :257
+        if not (disc >= 0.0 and enabled):                                   # :259-261
+            continue
+        sq = math.sqrt(disc)                                                # :263
+        root1 = (-half_b - sq) * inverse_a                                  # :270
+        root2 = (-half_b + sq) * inverse_a                                  # :271
+        root1_valid = t_min <= root1 < t_max                                # :272  simd_inside: >= start, < end
+        root2_valid = t_min <= root1 < t_max                                # :273  (sic: tests root1 again — SURVEY F4)
+        root = root1 if root1_valid else root2                              # :275  masked_select(root2, root1, root1_valid)
+        valid = (root1_valid or root2_valid) and enabled                    # :277
+        if valid and root <= best_t:                                        # :141  t.simd_le(self.t): the LAST object wins ties
+            loc = [o[k] + d[k] * root for k in range(3)]                    # :279  rays.at_t(root)  (src/ray.rs:102-104)
+            best_t, best_i, best_n = root, i, [loc[0] - cx, loc[1] - cy, loc[2] - cz]   # :280, :143-147
+    return best_i, best_t, best_n
+
+
+def finalize(o, d, t, n):              # src/objects.rs:157-162
+    ln = math.sqrt(p_length_squared(n))                                     # unit_vector: self / self.length()  (geometry.rs:439-446)
+    n = [x / ln for x in n]
+    p = [o[k] + d[k] * t for k in range(3)]                                 # rays.at_t(self.t)
+    front = p_dot(d, n) < 0.0                                               # directions.dot(normals) < 0
+    if not front:
+        n = [-x for x in n]
+    return p, n, front
+
+
+# ---- tests --------------------------------------------------------------------------------------------------------------
+def _scene():
+    rng = np.random.default_rng(20240611)
+    sph = [(0.0, -1000.0, 0.0, 1000.0)]
+    for _ in range(60):
+        sph.append((float(rng.uniform(-6, 6)), 0.2, float(rng.uniform(-6, 6)), 0.2))
+    sph += [(0.0, 1.0, 0.0, 1.0), (-4.0, 1.0, 0.0, 1.0), (4.0, 1.0, 0.0, 1.0)]
+    sph.append(sph[5])                                                       # an exact duplicate: the later index must win the tie
+    return sph
+
+
+def _rays(sph, m, seed):
+    rng = np.random.default_rng(seed)
+    rays = []
+    for k in range(m):
+        if k % 5 == 0:                                                       # from inside / on a sphere: near-root-only misses
+            c = sph[1 + k % 60]
+            o = [c[0] + 0.05, c[1], c[2]]
+        else:
+            o = [float(rng.uniform(-12, 12)), float(rng.uniform(0.05, 4.0)), float(rng.uniform(-12, 12))]
+        tgt = sph[int(rng.integers(0, len(sph)))]
+        d = [tgt[0] - o[0] + float(rng.normal(0, 0.2)), tgt[1] - o[1] + float(rng.normal(0, 0.2)), tgt[2] - o[2] + float(rng.normal(0, 0.2))]
+        s = float(rng.uniform(0.1, 2.0))                                     # directions are not unit in the reference
+        rays.append(o + [x * s for x in d])
+    return rays
+
+
+def test_sweep_agrees_with_the_cpp_oracle_bit_for_bit(oracle):
+    sph = _scene()
+    rays = _rays(sph, 240, 7)
+    enabled = [k % 11 != 3 for k in range(len(rays))]
+    idx, t = oracle.intersect(np.array(sph), np.array(rays), enabled=np.array(enabled, dtype=np.int32), f32=False)
+    n_hit = 0
+    for k, ry in enumerate(rays):
+        i, tt, _ = sweep(sph, ry[:3], ry[3:], enabled[k])
+        assert i == int(idx[k]), (k, i, int(idx[k]))
+        if i >= 0:
+            n_hit += 1
+            assert tt == float(t[k]), (k, tt, float(t[k]))                    # the same double, not merely close
+        else:
+            assert math.isinf(float(t[k]))
+    assert n_hit > 100
+    dup = len(sph) - 1                                                       # the duplicate of sphere 5: index 5 may never be reported
+    assert 5 not in set(int(i) for i in idx), dup                            # ... so index 5 is never reported
+
+
+@pytest.mark.parametrize("kind,hollow,param", [(1, 0, 0.0), (2, 0, 1.5), (2, 1, 1.5), (2, 0, 2.4)])
+def test_finalize_and_deterministic_scatter_agree_with_the_cpp_oracle(oracle, kind, hollow, param):
+    """Metal with fuzz 0 (reflect; the random term is multiplied by 0.0) and Dielectric (reflect / refract chosen by total
+    internal reflection or Schlick against the Fresnel draw, src/materials.rs:92-97, :128-147).  The draw is the third Philox
+    word as a 24-bit uniform — a definition of this build (the reference is OS-seeded) that the test takes as given."""
+    rng = np.random.default_rng(99 + kind * 10 + hollow)
+    sphere = (0.3, 0.9, -0.2, 1.1)
+    checked = 0
+    for k in range(120):
+        inside = kind == 2 and k % 3 == 0
+        if inside:
+            o = [sphere[0] + float(rng.uniform(-0.3, 0.3)), sphere[1] + float(rng.uniform(-0.3, 0.3)), sphere[2] + float(rng.uniform(-0.3, 0.3))]
+        else:
+            o = [float(rng.uniform(-5, 5)), float(rng.uniform(-1, 4)), float(rng.uniform(-5, 5))]
+        d = [sphere[i] - o[i] + float(rng.normal(0, 0.5)) for i in range(3)]
+        if inside:
+            d = [float(rng.normal(0, 1)) for _ in range(3)]
+        rnd = [int(x) for x in rng.integers(0, 2 ** 32, size=4)]
+        ref = oracle.hit_and_scatter(sphere, kind, hollow, (0.7, 0.6, 0.5), param, o + d, rnd, f32=False)
+        i, t, n = sweep([sphere], o, d)
+        assert (i >= 0) == ref["hit"]
+        if i < 0:
+            continue
+        p, nn, front = finalize(o, d, t, n)
+        assert t == ref["t"] and front == ref["front"]
+        assert p == list(ref["p"]) and nn == list(ref["n"])
+        if kind == 1:
+            refl = s_reflect(d, nn)
+            out = [refl[j] + 0.0 * 1.0 for j in range(3)]                    # + fuzzy_factor (0.0) * random_unit_vector
+            att = [0.7, 0.6, 0.5]
+        else:
+            ratio = 1.0 / param if front else param                          # :129
+            nrm = [-x for x in nn] if hollow else nn                         # :131
+            cos_theta = min(s_dot([-x for x in d], nrm), 1.0)                # :132
+            sin_theta = fsqrt(1.0 - cos_theta * cos_theta)                   # :133 (NaN when the un-normalised d gives |cos| > 1)
+            u = (rnd[2] >> 8) * 2.0 ** -24
+            if ratio * sin_theta > 1.0 or reflectance(cos_theta, ratio) > u:  # :135-137 (the draw happens only if it can refract)
+                out = s_reflect(d, nrm)
+            else:
+                out = s_refract(d, nrm, ratio)
+            att = [1.0, 1.0, 1.0]
+        assert list(ref["origin"]) == p
+        assert list(ref["attenuation"]) == att
+        got = list(ref["direction"])
+        if any(math.isnan(x) for x in out):
+            assert any(math.isnan(x) for x in got)                           # sqrt of a negative: un-normalised d can exceed |cos| <= 1
+        else:
+            assert out == got, (k, out, got)
+        checked += 1
+    assert checked > 40
+
+
+def test_reflectance_and_tie_rule_known_answers():
+    assert abs(reflectance(1.0, 1.5) - 0.04) < 1e-15                         # normal incidence, glass
+    two = [(0.0, 0.0, -1.0, 0.5), (0.0, 0.0, -1.0, 0.5)]
+    i, t, _ = sweep(two, [0.0, 0.0, 0.0], [0.0, 0.0, -1.0])
+    assert (i, t) == (1, 0.5)                                                # `<=`: last object wins
+    i, t, _ = sweep(two[:1], [0.0, 0.0, -1.0], [0.0, 0.0, -1.0])
+    assert i == -1                                                           # origin at the centre: root1 = -0.5, root2 never tried (F4)
+    i, t, _ = sweep(two[:1], [0.0, 0.0, 0.0], [0.0, 0.0, -2.0])
+    assert (i, t) == (0, 0.25)                                               # non-unit direction
