@@ -207,3 +207,61 @@ def test_reflectance_and_tie_rule_known_answers():
     assert i == -1                                                           # origin at the centre: root1 = -0.5, root2 never tried (F4)
     i, t, _ = sweep(two[:1], [0.0, 0.0, 0.0], [0.0, 0.0, -2.0])
     assert (i, t) == (0, 0.25)                                               # non-unit direction
+
+
+# ---- Camera::new (src/ray_tracing.rs:27-62), scalar Vec3 algebra (src/geometry.rs:105-131) ------------------------------
+def s_unit(v):                         # :117-119  self / self.length()
+    ln = math.sqrt(s_length_squared(v))
+    return [x / ln for x in v]
+
+
+def s_cross(a, b):                     # :125-131
+    return [a[1] * b[2] - a[2] * b[1], a[2] * b[0] - a[0] * b[2], a[0] * b[1] - a[1] * b[0]]
+
+
+def to_radians(deg):                   # f64::to_radians: value * (PI / 180)
+    return deg * (math.pi / 180.0)
+
+
+def camera_new(width, height, focal, view_angle, center, look_at, up, defocus_angle):
+    aspect = float(width) / float(height)                                        # :28
+    vh = math.tan(to_radians(view_angle) / 2.0) * focal * 2.0                    # :29
+    vw = vh * aspect                                                             # :32
+    direction = s_unit([look_at[i] - center[i] for i in range(3)])               # :34
+    w = [-x for x in direction]                                                  # :35
+    u = s_unit(s_cross(up, w))                                                   # :36
+    v = s_cross(w, u)                                                            # :37
+    vu = [x * vw for x in u]                                                     # :39
+    vv = [-x * vh for x in v]                                                    # :40
+    ulc = [center[i] - w[i] * focal - vu[i] / 2.0 - vv[i] / 2.0 for i in range(3)]   # :41
+    radius = focal * math.tan(to_radians(defocus_angle / 2.0))                   # :43
+    du = [radius * x for x in u]                                                 # :44
+    dv = [radius * x for x in v]                                                 # :45
+    return center + ulc + vu + vv + du + dv
+
+
+@pytest.mark.parametrize("args", [
+    (3840, 2160, 10.0, 30.0, [16.0, 2.0, 18.5], [0.0, 0.0, 0.0], [0.0, 1.0, 0.0], 0.0),      # the camera main hard-codes, src/main.rs:45-58
+    (400, 225, 10.0, 20.0, [13.0, 2.0, 3.0], [0.0, 0.0, 0.0], [0.0, 1.0, 0.0], 0.6),
+    (1921, 1079, 3.7, 71.3, [-2.5, 7.25, 0.125], [1.0, -0.5, 9.0], [0.1, 1.0, -0.2], 2.5),
+])
+def test_camera_new_agrees_with_the_cpp_oracle_and_the_library(oracle, rtb, args):
+    want = camera_new(*[list(a) if isinstance(a, list) else a for a in args])
+    got = list(oracle.camera_new(*args))
+    assert got == want                                                            # 18 doubles, bit for bit
+    cam = rtb.Camera(*args)                                                       # rtb200_camera_init: the product's Camera::new (host arithmetic)
+    assert list(cam.vectors()) == want
+
+
+def test_sky_and_quantiser_agree_with_the_cpp_oracle(oracle):
+    rng = np.random.default_rng(5)
+    for _ in range(200):
+        d = [float(x) for x in rng.normal(0, 1.5, size=3)]
+        a = (d[1] + 1.0) * 0.5                                                    # src/ray_tracing.rs:365
+        w = -a + 1.0                                                              # :366  white * (-a + 1.0)
+        want = [1.0 * w + 0.5 * a, 1.0 * w + 0.7 * a, 1.0 * w + 1.0 * a]          # :366-368
+        assert list(oracle.sky(d, f32=False)) == want
+    for c in [0.0, 1.0, 0.25, 2.0, 1e-9, 0.999, 0.5, float("nan"), -0.1] + [float(x) for x in rng.uniform(0, 1.2, size=200)]:
+        v = fsqrt(c) * 255.999                                                    # src/color.rs:58-61: (sqrt(c) * 255.999) as u8
+        want = 0 if not (v >= 0.0) else 255 if v >= 255.0 else int(v)             # Rust `as u8`: truncates, saturates, NaN -> 0
+        assert oracle.quantise(c, f32=False) == want, c
