@@ -61,3 +61,21 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle" not in text.lower() or f == "rt_device.cuh", f"{f} mentions the oracle"
+
+
+def test_null_context_is_an_error_on_every_device_entry_point(rtb):
+    """Argument validation runs before any CUDA call: a null context is RTB200_ERR_INVALID on a box without a GPU too
+    (nothing aborts across the ABI).  Covers rtb200_trace_device_static, the entry point without a reference counterpart."""
+    import ctypes as C
+    lib, A = rtb._abi.lib, rtb._abi
+    cam = rtb.Camera.default(16, 9)
+    p = A.Params(5, 2, 1, 0, 2, 0, 9, 0, 1)
+    used = C.c_uint64(123)
+    assert lib.rtb200_trace_device_static(None, C.byref(cam.abi), C.byref(p), None, None, C.byref(used)) == A.ERR_INVALID
+    assert lib.rtb200_trace_device(None, C.byref(cam.abi), C.byref(p), None, None) == A.ERR_INVALID
+    assert lib.rtb200_render(None, C.byref(cam.abi), C.byref(p), None, None, None) == A.ERR_INVALID
+    assert lib.rtb200_device_free(None, None) == A.ERR_INVALID and lib.rtb200_ipc_close(None, None) == A.ERR_INVALID
+    assert b"null" in lib.rtb200_last_error() or b"ctx" in lib.rtb200_last_error()
+    assert A.STATIC_SCRATCH_BYTES == 32 << 20
+    header = open(os.path.join(ROOT, "include", "rtb200.h")).read()
+    assert "#define RTB200_STATIC_SCRATCH_BYTES %d" % A.STATIC_SCRATCH_BYTES in header
