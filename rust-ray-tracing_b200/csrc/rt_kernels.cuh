@@ -452,6 +452,7 @@ __device__ __forceinline__ void drain_pending(uint32_t pend, int first_sphere, c
 template <class PV_T>
 struct ParamSlab {
     static constexpr bool overflow_by_call = false;   // refine_chunk: keep the chunk loop free of calls (uniform datapath)
+    static constexpr int max_tail_groups = 3;         // sweep_two_stage: the last block takes the short path up to 24 existing spheres
     const PV_T& pv;
     template <int RAYS>
     __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
@@ -465,12 +466,35 @@ struct ParamSlab {
             for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.y, C.x, C.y)), mask[r], 1);
         }
     }
+    // The scene's LAST block when fewer than 25 of its 32 spheres exist (the arrays are padded to whole blocks with
+    // never-candidates): only the first `groups` (1..3) groups of 8 spheres are evaluated — a rolled loop over 8-sphere bodies,
+    // still uniform control flow — and the rest of the mask word is filled with "not a candidate".  C2/T/C5 have 486/485
+    // spheres = 15 blocks + 6 (5) spheres: the 16th block costs 79 instead of 319 instructions, 2.9 % of a loop trip.
+    template <int RAYS>
+    __device__ __forceinline__ void partial(int blk, int groups, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
+        const int pair0 = blk * (SWEEP_BLOCK / 2);
+#pragma unroll 1
+        for (int g = 0; g < groups; g++) {
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float2 A = pv.s1[3 * (pair0 + g * 4 + j)], B = pv.s1[3 * (pair0 + g * 4 + j) + 1], C = pv.s1[3 * (pair0 + g * 4 + j) + 2];
+#pragma unroll
+                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, B.x)), mask[r], 1);
+#pragma unroll
+                for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.y, C.x, C.y)), mask[r], 1);
+            }
+        }
+        const int sh = SWEEP_BLOCK - 8 * groups;             // 8, 16 or 24 spheres not evaluated: never candidates
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = (mask[r] << sh) | ((1u << sh) - 1u);
+    }
 };
 
 // SmemSlab: the same triples staged in shared memory (scenes too large for parameter space): three LDS.128 broadcasts
 // per four spheres, each serving the RAYS rays of the lane.
 struct SmemSlab {
     static constexpr bool overflow_by_call = true;
+    static constexpr int max_tail_groups = 2;         // (the rolled LDS loop pays for itself up to 16 existing spheres)
     const float4* s;
     template <int RAYS>
     __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
@@ -488,6 +512,26 @@ struct SmemSlab {
             for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], C.y, C.z, C.w)), mask[r], 1);
         }
     }
+    // the scene's last, mostly empty block (see ParamSlab::partial): `groups` (1..3) groups of 8 spheres
+    template <int RAYS>
+    __device__ __forceinline__ void partial(int blk, int groups, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
+        const float4* q = s + blk * (SWEEP_BLOCK / 4 * 3);
+#pragma unroll 1
+        for (int j = 0; j < 2 * groups; j++) {
+            const float4 A = q[3 * j], B = q[3 * j + 1], C = q[3 * j + 2];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, A.z)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.w, B.x, B.y)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.z, B.w, C.x)), mask[r], 1);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], C.y, C.z, C.w)), mask[r], 1);
+        }
+        const int sh = SWEEP_BLOCK - 8 * groups;
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) mask[r] = (mask[r] << sh) | ((1u << sh) - 1u);
+    }
 };
 
 template <int RAYS, class S1, class RaySrc>
@@ -495,15 +539,20 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
                                                 const double4* __restrict__ g_exact, float h_bound, int count, uint32_t* masks, int stride,
                                                 const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     const int n_blocks = (count + SWEEP_BLOCK - 1) / SWEEP_BLOCK;     // the stage-1 array is padded to whole blocks
+    // groups of 8 spheres that exist in the scene's last block; 1..3: that block takes the short path (S1::partial)
+    const int tail_groups = ((count & (SWEEP_BLOCK - 1)) + 7) >> 3;
+    const bool short_tail = tail_groups >= 1 && tail_groups <= S1::max_tail_groups;
     for (int cb = 0; cb < n_blocks; cb += 8) {
         const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
+        const bool tail_here = short_tail && cb + nb == n_blocks;
+        const int nb_full = tail_here ? nb - 1 : nb;
         uint32_t todo[RAYS];
 #pragma unroll
         for (int r = 0; r < RAYS; r++) todo[r] = 0u;
         // ---- stage 1 ----
         uint32_t bit = 1u;
 #pragma unroll 1
-        for (int b = 0; b < nb; b++, bit <<= 1) {
+        for (int b = 0; b < nb_full; b++, bit <<= 1) {
             uint32_t mask[RAYS];
 #pragma unroll
             for (int r = 0; r < RAYS; r++) mask[r] = 0;
@@ -511,6 +560,17 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
                 masks[(r * 8 + b) * stride] = mask[r];
+                todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
+            }
+        }
+        if (tail_here) {
+            uint32_t mask[RAYS];
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) mask[r] = 0;
+            s1.template partial<RAYS>(cb + nb_full, tail_groups, sl, mask);
+#pragma unroll
+            for (int r = 0; r < RAYS; r++) {
+                masks[(r * 8 + nb_full) * stride] = mask[r];
                 todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
             }
         }
