@@ -359,18 +359,27 @@ struct Best { double t; int i; };                          // the running closes
 // Next stage-1 candidate of the walk.  maddr = shared-memory byte address of the ray's mask word of the
 // chunk's block 0 (block b's word lies stride_bytes * b further); todo = bitmap of the blocks that hold candidates; the
 // block index comes from that per-lane bitmap, highest block first (the visiting order is free: test_candidate's update
-// rule does not depend on it).  base31 = index of sphere 31 of block 0.
+// rule does not depend on it).
 __device__ __forceinline__ void walk_next(uint32_t maddr, uint32_t stride_bytes, uint32_t& todo, uint32_t& cand, int& last, int base31, int& idx) {
-    uint32_t hi, bit;                                      // precondition: (cand | todo) != 0
-    if (cand == 0u) {
-        uint32_t w;
-        asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(todo));   // FLO / BMSK: one instruction each
-        asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
-        todo ^= bit;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(maddr + hi * stride_bytes));
-        cand = ~w;                                         // not empty: stage 1 set the block's bit
-        last = base31 + (int)(hi * SWEEP_BLOCK);
-    }
+    // precondition: (cand | todo) != 0.  last = index of sphere 31 of the current block; base31 = that of the chunk's block 0.
+    uint32_t hi, bit;
+    // Refill without a branch: with ~1.1 candidates per block some lane of the warp needs the next block's mask word on
+    // nearly every step, so the branch (ISETP + BSSY + BRA + BSYNC around 8 instructions) was taken anyway; predicated, the
+    // refill costs its 8 instructions and no control flow.  bfind(0) = 0xffffffff only when no refill is needed (precondition).
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b32 hb, bb, w, a;\n\t"
+        "setp.eq.u32 p, %1, 0;\n\t"
+        "bfind.u32 hb, %0;\n\t"
+        "bmsk.clamp.b32 bb, hb, 1;\n\t"
+        "mad.lo.u32 a, hb, %4, %3;\n\t"
+        "@p ld.shared.u32 w, [a];\n\t"
+        "@p not.b32 %1, w;\n\t"
+        "@p xor.b32 %0, %0, bb;\n\t"
+        "@p shl.b32 a, hb, 5;\n\t"
+        "@p add.s32 %2, a, %5;\n\t"
+        "}"
+        : "+r"(todo), "+r"(cand), "+r"(last)
+        : "r"(maddr), "r"(stride_bytes), "r"(base31));
     asm("bfind.u32 %0, %1;" : "=r"(hi) : "r"(cand));       // sphere j of the block sits at bit 31 - j
     asm("bmsk.clamp.b32 %0, %1, 1;" : "=r"(bit) : "r"(hi));
     cand ^= bit;
@@ -420,7 +429,7 @@ __device__ RTB_REFINE_INLINE void refine_chunk(const uint32_t* masks_r, int stri
         float h;
         const float q = filter_value_h(f, fs.x, fs.y, fs.z, fs.w, h);                              // stage 2 (FP32, conservative)
         if (!(__float_as_uint(q) >> 31) && !(h < h_min)) {
-            if (pend < PEND_FULL) pend = (pend << 9) | (uint32_t)(idx - first_sphere + (r << 8));  // park it for drain_pending
+            if (pend < PEND_FULL) pend = ((pend << 9) + (uint32_t)(r << 8)) | ((uint32_t)idx & 255u);   // park it for drain_pending (chunks start at multiples of 256)
             else if (CALL_OVERFLOW) best = stage3_now(rays.load(r), load_exact(&g_exact[idx]), idx, best);   // the lane's fourth: now
             else test_candidate(promote_ray(rays.load(r)), rays.both_roots(), load_exact(&g_exact[idx]), idx, best.t, best.i);
         }
@@ -490,47 +499,50 @@ struct ParamSlab {
     }
 };
 
-// SmemSlab: the same triples staged in shared memory (scenes too large for parameter space): three LDS.128 broadcasts
+// SmemSlab: the stage-1 data staged in shared memory (scenes too large for parameter space): three LDS.128 broadcasts
 // per four spheres, each serving the RAYS rays of the lane.
+// Layout per four spheres: {c_a x4}, {c_b x4}, {-R'' x4} (R'' = R' stepped one ulp up, negated, by the host), evaluated with
+// the packed FP32 FMA of sm_100 (fma.rn.f32x2: two spheres of one ray per instruction).  With the sphere in VECTOR registers
+// (from LDS.128) a scalar chain FFMA reads three distinct registers and loses a cycle to the two-bank register file on
+// every other instruction (0.36 dispatch stalls per issue on C4); the packed form reads three 64-bit pairs in the two
+// cycles it occupies anyway.  Per element the arithmetic is the scalar one: p = fma(c_a, U_a, fma(c_b, U_b, -o.U)), then
+// q' = fma(p, p, -R'') = -(R'' - p^2): sign bit SET <=> candidate, and p^2 <= R' implies p^2 < R'' (exact difference
+// negative, so the rounded one is negative and non-zero): every candidate of the scalar test is a candidate here.
 struct SmemSlab {
     static constexpr bool overflow_by_call = true;
-    static constexpr int max_tail_groups = 2;         // (the rolled LDS loop pays for itself up to 16 existing spheres)
+    static constexpr int max_tail_groups = 2;
     const float4* s;
+    template <int RAYS>
+    __device__ __forceinline__ void quad(const float4 A, const float4 B, const float4 C, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
+#pragma unroll
+        for (int r = 0; r < RAYS; r++) {
+            const float2 ua = make_float2(sl[r].ua, sl[r].ua), ub = make_float2(sl[r].ub, sl[r].ub), nou = make_float2(sl[r].nou, sl[r].nou);
+            const float2 p01 = __ffma2_rn(make_float2(A.x, A.y), ua, __ffma2_rn(make_float2(B.x, B.y), ub, nou));
+            const float2 p23 = __ffma2_rn(make_float2(A.z, A.w), ua, __ffma2_rn(make_float2(B.z, B.w), ub, nou));
+            const float2 q01 = __ffma2_rn(p01, p01, make_float2(C.x, C.y)), q23 = __ffma2_rn(p23, p23, make_float2(C.z, C.w));
+            mask[r] = __funnelshift_l(__float_as_uint(q01.x), mask[r], 1);
+            mask[r] = __funnelshift_l(__float_as_uint(q01.y), mask[r], 1);
+            mask[r] = __funnelshift_l(__float_as_uint(q23.x), mask[r], 1);
+            mask[r] = __funnelshift_l(__float_as_uint(q23.y), mask[r], 1);
+        }
+    }
     template <int RAYS>
     __device__ __forceinline__ void block(int blk, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
         const float4* q = s + blk * (SWEEP_BLOCK / 4 * 3);
 #pragma unroll
-        for (int j = 0; j < SWEEP_BLOCK / 4; j++) {
-            const float4 A = q[3 * j], B = q[3 * j + 1], C = q[3 * j + 2];
+        for (int j = 0; j < SWEEP_BLOCK / 4; j++) quad<RAYS>(q[3 * j], q[3 * j + 1], q[3 * j + 2], sl, mask);
 #pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, A.z)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.w, B.x, B.y)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.z, B.w, C.x)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], C.y, C.z, C.w)), mask[r], 1);
-        }
+        for (int r = 0; r < RAYS; r++) mask[r] = ~mask[r];     // the callers' polarity: bit set = not a candidate
     }
     // the scene's last, mostly empty block (see ParamSlab::partial): `groups` (1..3) groups of 8 spheres
     template <int RAYS>
     __device__ __forceinline__ void partial(int blk, int groups, const SlabRay (&sl)[RAYS], uint32_t (&mask)[RAYS]) const {
         const float4* q = s + blk * (SWEEP_BLOCK / 4 * 3);
 #pragma unroll 1
-        for (int j = 0; j < 2 * groups; j++) {
-            const float4 A = q[3 * j], B = q[3 * j + 1], C = q[3 * j + 2];
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.x, A.y, A.z)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], A.w, B.x, B.y)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], B.z, B.w, C.x)), mask[r], 1);
-#pragma unroll
-            for (int r = 0; r < RAYS; r++) mask[r] = __funnelshift_l(__float_as_uint(slab_value(sl[r], C.y, C.z, C.w)), mask[r], 1);
-        }
+        for (int j = 0; j < 2 * groups; j++) quad<RAYS>(q[3 * j], q[3 * j + 1], q[3 * j + 2], sl, mask);
         const int sh = SWEEP_BLOCK - 8 * groups;
 #pragma unroll
-        for (int r = 0; r < RAYS; r++) mask[r] = (mask[r] << sh) | ((1u << sh) - 1u);
+        for (int r = 0; r < RAYS; r++) mask[r] = (~mask[r] << sh) | ((1u << sh) - 1u);
     }
 };
 
@@ -913,7 +925,7 @@ struct WarpChunk { uint32_t next = 0, end = 0; };   // the warp's private slice 
 
 template <bool STRIDED>
 __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConsts& C, PathSlot& q, bool swept, float best_t, int best_i,
-                                          bool& exhausted, WarpChunk& chunk, unsigned& n_segments, unsigned& n_paths, unsigned lane) {
+                                          bool& exhausted, WarpChunk& chunk, unsigned& n_segments, unsigned lane) {
     // ---- 1. terminate (src/ray_tracing.rs:353-357, :365-370) ----
     if (swept && q.has_path) {
         n_segments++;
@@ -971,11 +983,8 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
                 q.item = item;
                 q.s = split_sample(P, C, item & C.split_mask);
                 q.acc = mk3(0.f, 0.f, 0.f);
-                if (P.max_bounces <= 0) {              // `for _ in 0..0`: every ray stays enabled => black (:370)
-                    const int s_end = split_sample(P, C, (item & C.split_mask) + 1);
-                    n_paths += (unsigned)(s_end - q.s);
-                    q.s = s_end;
-                }
+                if (P.max_bounces <= 0)                // `for _ in 0..0`: every ray stays enabled => black (:370)
+                    q.s = split_sample(P, C, (item & C.split_mask) + 1);
             }
         }
         const uint32_t n_need = (uint32_t)__popc(need_mask);
@@ -998,7 +1007,6 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
             q.thr = mk3(1.f, 1.f, 1.f);
             q.bounce = 0;
             q.has_path = true;
-            n_paths++;
         } else {                                       // finalize + Material::get_hit_result (src/ray_tracing.rs:335-346)
             float4 sp = __ldg(&P.spheres[best_i]);
             HitRec rec = finalize_hit(q.o, q.d, best_t, mk3(sp.x, sp.y, sp.z));
@@ -1012,18 +1020,15 @@ __device__ __forceinline__ void slot_step(const TraceParams& P, const TraceConst
     }
 }
 
-// Adds a warp's per-lane path/segment counts to the launch counters: one atomic pair per warp.
-__device__ __forceinline__ void flush_counters(const TraceParams& P, unsigned n_paths, unsigned n_segments, unsigned lane) {
-    unsigned long long seg64 = n_segments, path64 = n_paths;
+// Adds a warp's per-lane segment counts to the launch counters (one atomic per warp).  The number of PATHS needs no
+// counting: every sample of every traced pixel starts exactly one path (src/renderer.rs:148-160), so the launch's first
+// thread adds n_pix x n_samples (a per-lane path counter cost a register the kernels do not have to spare).
+__device__ __forceinline__ void flush_counters(const TraceParams& P, const TraceConsts& C, unsigned n_segments, unsigned lane) {
+    unsigned long long seg64 = n_segments;
 #pragma unroll
-    for (int sh = 16; sh > 0; sh >>= 1) {
-        seg64 += __shfl_xor_sync(0xffffffffu, seg64, sh);
-        path64 += __shfl_xor_sync(0xffffffffu, path64, sh);
-    }
-    if (lane == 0) {
-        atomicAdd(&P.counters[0], path64);
-        atomicAdd(&P.counters[1], seg64);
-    }
+    for (int sh = 16; sh > 0; sh >>= 1) seg64 += __shfl_xor_sync(0xffffffffu, seg64, sh);
+    if (lane == 0) atomicAdd(&P.counters[1], seg64);
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&P.counters[0], (unsigned long long)C.n_pix * C.n_samples);
 }
 
 // K2, resident variant: path state in registers, filter spheres staged in shared memory.  Any scene that fits the
@@ -1046,7 +1051,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
     for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
     bool exhausted = false;
     WarpChunk chunk;
-    unsigned n_segments = 0, n_paths = 0;          // per-lane counts (a lane traces far fewer than 2^32 segments)
+    unsigned n_segments = 0;                       // per-lane count (a lane traces far fewer than 2^32 segments)
     float best_t[RAYS];
     int best_i[RAYS];
 #pragma unroll
@@ -1057,7 +1062,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -1083,7 +1088,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);   // the f64 root, rounded once for the FP32 path state
         swept = true;
     }
-    flush_counters(P, n_paths, n_segments, lane);
+    flush_counters(P, C, n_segments, lane);
 }
 
 // K2, large scenes: two-stage sweep with the stage-1 triples staged in shared memory and the path state of the RAYS
@@ -1109,7 +1114,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
     for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
     bool exhausted = false;
     WarpChunk chunk;
-    unsigned n_segments = 0, n_paths = 0;
+    unsigned n_segments = 0;
     float best_t[RAYS];
     int best_i[RAYS];
 #pragma unroll
@@ -1119,7 +1124,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -1146,7 +1151,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
     }
-    flush_counters(P, n_paths, n_segments, lane);
+    flush_counters(P, C, n_segments, lane);
 }
 
 // K2, scenes of ANY size: k_trace_paths_l with the stage-1 triples streamed per warp from global memory
@@ -1168,7 +1173,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
     for (int r = 0; r < RAYS; r++) slot_reset(slot[r]);
     bool exhausted = false;
     WarpChunk chunk;
-    unsigned n_segments = 0, n_paths = 0;
+    unsigned n_segments = 0;
     float best_t[RAYS];
     int best_i[RAYS];
 #pragma unroll
@@ -1178,7 +1183,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
         bool any_path = false, idle = true;
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
-            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, slot[r], swept, best_t[r], best_i[r], exhausted, chunk, n_segments, lane);
             any_path = any_path || slot[r].has_path;
             idle = idle && slot[r].item == NO_ITEM;
         }
@@ -1205,7 +1210,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_g(const __grid_const
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
     }
-    flush_counters(P, n_paths, n_segments, lane);
+    flush_counters(P, C, n_segments, lane);
 }
 
 // K2, parameter-space variant (scenes of at most N spheres): the filter spheres are kernel parameters, so the sweep's
@@ -1265,7 +1270,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
     bool exhausted = false;
     WarpChunk chunk;
     RTB_TL_START(lane);
-    unsigned n_segments = 0, n_paths = 0;
+    unsigned n_segments = 0;
     bool swept = false;
 
     for (;;) {
@@ -1278,7 +1283,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             q.item = W(12, r); q.s = (int)W(13, r);
             const uint32_t bw = W(14, r);
             q.bounce = (int)(bw & 0x7fffffffu); q.has_path = (bw >> 31) != 0u;
-            slot_step<STRIDED>(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, chunk, n_segments, n_paths, lane);
+            slot_step<STRIDED>(P, C, q, swept, F(15, r), (int)W(16, r), exhausted, chunk, n_segments, lane);
             W(0, r) = __float_as_uint(q.o.x); W(1, r) = __float_as_uint(q.o.y); W(2, r) = __float_as_uint(q.o.z);
             W(3, r) = __float_as_uint(q.d.x); W(4, r) = __float_as_uint(q.d.y); W(5, r) = __float_as_uint(q.d.z);
             W(6, r) = __float_as_uint(q.thr.x); W(7, r) = __float_as_uint(q.thr.y); W(8, r) = __float_as_uint(q.thr.z);
@@ -1326,7 +1331,7 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
         swept = true;
     }
     RTB_TL_EXIT(lane);
-    flush_counters(P, n_paths, n_segments, lane);
+    flush_counters(P, C, n_segments, lane);
 }
 // ---- combine: accum[row range] = sum_k partial[k] in plane order (deterministic) -----------------------------------
 // out = the image at the launch's first traced row; width / row_skip map a local pixel to its image pixel when the traced

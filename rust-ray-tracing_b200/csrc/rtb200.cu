@@ -69,7 +69,8 @@ struct rtb200_ctx {
     float4* d_mat = nullptr;
     int* d_mat_kind = nullptr;
     double4* d_exact = nullptr;                        // {cx, cy, cz, r*r} in f64, list order, padded: the exact candidate test of every sweep
-    float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (shared-memory two-stage variant)
+    float4* d_slab = nullptr;                          // stage-1 triples, n_padded * 3 floats (k_filter_check; the parameter-space kernels take h_slab)
+    float4* d_slabq = nullptr;                         // the same in SmemSlab's layout (shared-memory and streamed two-stage kernels)
     int n_padded = 32;
     float h_bound = 0.0f;                              // max |c| + r over the scene, rounded up (TraceParams::h_bound)
     int largest_sphere = 0;                            // index of the sphere with the largest radius (rtb200_filter_check)
@@ -295,7 +296,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto launch_streamed = [&]() {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
-        pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
+        pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slabq;
         const size_t smem_g = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)(LRT / 32) * 2 * rtb::STREAM_CHUNK_F4 * sizeof(float4);
         k_g<<<sms, LRT, smem_g, st>>>(pl);
     };
@@ -327,7 +328,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     } else if (two_stage_smem) {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
-        pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slab;
+        pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slabq;
         const size_t smem_slr = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
         if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) {
             ctx->last_kernel = "k_trace_paths_l<640,2> (two-stage, stage-1 triples staged in shared memory, path state in registers)";
@@ -512,6 +513,7 @@ struct HostScene {
     size_t off_sph = 0, off_flt = 0, off_mat = 0, off_slab = 0, off_kind = 0;
     std::vector<float4> filter;                        // n entries (kernel-parameter variant of the one-stage sweep)
     std::vector<float> slab;                           // cnt * 3 (kernel-parameter variant of the two-stage sweep)
+    size_t off_slabq = 0;                              // the same data for the shared-memory kernels (SmemSlab's layout)
     int up_axis = 1, largest = 0;
     float rp_min = 1.0f, h_bound = 0.0f;
     double slab_pass = 1.0;
@@ -589,13 +591,23 @@ static int build_host_scene(const rtb200_scene* scene, HostScene& hs) {
     hs.n = n; hs.cnt = cnt;
     hs.off_sph = cnt * sizeof(double4); hs.off_flt = hs.off_sph + cnt * sizeof(float4); hs.off_mat = hs.off_flt + cnt * sizeof(float4);
     hs.off_slab = hs.off_mat + cnt * sizeof(float4); hs.off_kind = hs.off_slab + cnt * 3 * sizeof(float);
-    hs.arena.resize(hs.off_kind + cnt * sizeof(int));      // cnt is a multiple of 32, so every array starts 32-byte aligned
+    hs.off_slabq = hs.off_kind + cnt * sizeof(int);
+    hs.arena.resize(hs.off_slabq + cnt * 3 * sizeof(float));   // cnt is a multiple of 32, so every array starts 32-byte aligned
     std::memcpy(hs.arena.data(), ex.data(), cnt * sizeof(double4));
     std::memcpy(hs.arena.data() + hs.off_sph, sph.data(), cnt * sizeof(float4));
     std::memcpy(hs.arena.data() + hs.off_flt, flt.data(), cnt * sizeof(float4));
     std::memcpy(hs.arena.data() + hs.off_mat, mat.data(), cnt * sizeof(float4));
     std::memcpy(hs.arena.data() + hs.off_slab, hs.slab.data(), cnt * 3 * sizeof(float));
     std::memcpy(hs.arena.data() + hs.off_kind, kind.data(), cnt * sizeof(int));
+    {   // SmemSlab's layout (rt_kernels.cuh): per four spheres {c_a x4}, {c_b x4}, {-R'' x4}, R'' = R' one ulp up
+        float* q = reinterpret_cast<float*>(hs.arena.data() + hs.off_slabq);
+        for (size_t g = 0; g < cnt / 4; g++)
+            for (int k = 0; k < 4; k++) {
+                const float* t = &hs.slab[(g * 4 + k) * 3];
+                q[g * 12 + k] = t[0]; q[g * 12 + 4 + k] = t[1];
+                q[g * 12 + 8 + k] = -std::nextafterf(t[2], INFINITY);      // padding: R' = -inf -> -R'' = +max: never a candidate
+            }
+    }
     hs.filter.assign(flt.begin(), flt.begin() + n);
     hs.largest = 0;
     double hb = 0.0;
@@ -616,7 +628,7 @@ static int commit_host_scene(rtb200_ctx* ctx, const HostScene& hs, cudaStream_t 
     if (ctx->scene_capacity < bytes) {
         cudaFree(ctx->d_scene);
         ctx->d_scene = nullptr; ctx->scene_capacity = 0;
-        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr; ctx->d_exact = nullptr;
+        ctx->d_spheres = nullptr; ctx->d_filter = nullptr; ctx->d_mat = nullptr; ctx->d_mat_kind = nullptr; ctx->d_slab = nullptr; ctx->d_slabq = nullptr; ctx->d_exact = nullptr;
         CU_TRY(cudaMalloc(&ctx->d_scene, bytes));
         ctx->scene_capacity = bytes;
     }
@@ -628,6 +640,7 @@ static int commit_host_scene(rtb200_ctx* ctx, const HostScene& hs, cudaStream_t 
     ctx->d_filter = reinterpret_cast<float4*>(base + hs.off_flt);
     ctx->d_mat = reinterpret_cast<float4*>(base + hs.off_mat);
     ctx->d_slab = reinterpret_cast<float4*>(base + hs.off_slab);
+    ctx->d_slabq = reinterpret_cast<float4*>(base + hs.off_slabq);
     ctx->d_mat_kind = reinterpret_cast<int*>(base + hs.off_kind);
     ctx->n_padded = (int)hs.cnt;
     ctx->n_spheres = hs.n;
