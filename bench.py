@@ -474,8 +474,8 @@ def run_ours(args):
             t = json.load(f).get(args.workload)
         if t and not args.spp and world == 1:
             traffic = t.get("dram_bytes_per_launch")
-            executed = {k: t[k] for k in ("kernel", "issue_slots_busy_pct", "fma_pipe_pct", "alu_pipe_pct", "fp64_pipe_pct", "threads_per_instruction",
-                                          "warp_instructions", "source") if k in t}
+            executed = {k: t[k] for k in ("kernel", "issue_slots_busy_pct", "issue_cycles_busy_pct", "fma_pipe_pct", "fma_pipe_cycles_active_pct", "alu_pipe_pct",
+                                          "fp64_pipe_pct", "threads_per_instruction", "warp_instructions", "note", "source") if k in t}
     except Exception:
         traffic = None
 

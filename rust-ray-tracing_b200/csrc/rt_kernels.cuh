@@ -791,7 +791,7 @@ struct TraceParamsV {
 
 // TraceParams + the STAGE-1 (slab test, rt_filter.h) spheres in parameter space: three floats {c_a, c_b, R'} per sphere
 // with the scene's `up` axis dropped, two spheres per three float2 (LDCU.64 x3 per pair), padded to a multiple of 32
-// spheres with never-candidates (R' = -inf).  Up to N spheres (N = 512 / 768: the triples must stay resident in the constant cache, see launch_trace).
+// spheres with never-candidates (R' = -inf).  Up to N = 512 spheres (the triples must stay resident in the constant cache, see launch_trace).
 template <int N>
 struct TraceParamsS {
     static constexpr bool two_stage = true;
@@ -805,7 +805,7 @@ struct TraceParamsS {
 };
 
 // TraceParams + a pointer to the stage-1 triples in global memory: the kernel stages them in SHARED memory (scenes of
-// more than 768 spheres, up to what fits beside the path state: ~10 600 spheres).
+// more than 512 spheres, up to what fits beside the path state: ~10 600 spheres).
 struct TraceParamsL {
     static constexpr bool two_stage = true;
     static constexpr bool s1_smem = true;

@@ -233,7 +233,6 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     using PV512 = rtb::TraceParamsV<512>;
     using PV1024 = rtb::TraceParamsV<1024>;
     using PS512 = rtb::TraceParamsS<512>;
-    using PS768 = rtb::TraceParamsS<768>;
     // Every trace kernel exists in two instantiations: contiguous band (STRIDED = false: every single-GPU render) and
     // interleaved scanlines (row_stride > 1).  KSEL picks by this launch's stride.
     const bool strided = row_stride > 1;
@@ -245,7 +244,6 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     auto k_v512 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PV512);
     auto k_v1024 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PV1024);
     auto k_s512 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS512);
-    auto k_s768 = KSEL(k_trace_paths_v<VT, 4, VR, CV, PS768);
     auto k_sl = KSEL(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
     auto k_slr = KSEL(k_trace_paths_l<LRT, LR);
     auto k_g = KSEL(k_trace_paths_g<LRT, LR);          // any scene size: stage-1 triples streamed per warp from global memory
@@ -255,7 +253,6 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         KBOTH(k_trace_paths_v<VT, 4, VR, CV, PV512);
         KBOTH(k_trace_paths_v<VT, 4, VR, CV, PV1024);
         KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS512);
-        KBOTH(k_trace_paths_v<VT, 4, VR, CV, PS768);
         KBOTH(k_trace_paths_v<LT, 1, VR, CV, rtb::TraceParamsL);
         KBOTH(k_trace_paths_l<LRT, LR);
         KBOTH(k_trace_paths_g<LRT, LR);
@@ -274,13 +271,14 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     const bool fits_v = want != 1 && (smem_v + 1024) * 4 <= per_sm;
     // two-stage (slab test first) when the scene's layout lets stage 1 reject most pairs; RTB200_FLAG_ONE_STAGE forces
     // the single-stage parameter-space kernel, RTB200_FLAG_TWO_STAGE the two-stage one.
-    // Stage-1 triples go through kernel parameter space (uniform-register operands) only while they stay resident in
-    // the SM's constant cache: up to PARAM_MAX = 768 spheres (9 KB).  Measured on jittered-grid scenes (1920x1080x16 spp,
-    // parameter space vs staged in shared memory): 257 spheres 5.03 vs 4.52 ms, 485: 8.23 vs 7.47, 785: 12.2 vs 11.9,
-    // 1297: 24.3 vs 18.9, 1937: 40.4 vs 26.1, 2501: 56.8 vs 33.0 — the indexed LDCU sweep thrashes the constant cache
-    // beyond ~10 KB; C2 (486 spheres, 100 spp): 44.75 vs 46.6 ms in favour of parameter space.  RTB200_PARAM_MAX
-    // overrides (tuning aid).
-    constexpr int PARAM_MAX = 768;
+    // Stage-1 triples go through kernel parameter space (uniform-register operands) for scenes of up to PARAM_MAX = 512
+    // spheres (6 KB: they must stay resident in the SM's constant cache; beyond ~10 KB the indexed LDCU sweep thrashes
+    // it: 1 297 spheres 24.3 vs 18.9 ms, 2 501: 56.8 vs 33.0).  Larger scenes stage them in shared memory and run the
+    // packed-FMA stage 1 (SmemSlab), which since round 2 is as fast per pair as the uniform-operand form: 485 / 577 / 677
+    // spheres at 64 spp, parameter space vs shared memory: 26.46 / 32.34 / 37.52 vs 26.56 / 32.08 / 36.98 ms; C2 (486
+    // spheres, 100 spp) 43.55 vs 44.11, T 425.2 vs 430.5 in favour of parameter space (eight warps per sub-partition hide
+    // the refine walks better than five).  RTB200_PARAM_MAX overrides (tuning aid).
+    constexpr int PARAM_MAX = 512;
     int param_max = PARAM_MAX;
     if (const char* e = std::getenv("RTB200_PARAM_MAX")) { int v = std::atoi(e); if (v >= 0 && v <= PARAM_MAX) param_max = v; }
     const bool two_stage = fits_v && P.n_spheres <= param_max && !(p->flags & RTB200_FLAG_ONE_STAGE) &&
@@ -315,16 +313,11 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
     if (streamed) {
         ctx->last_kernel = "k_trace_paths_g<640,2> (two-stage, stage-1 triples streamed per warp from global memory)";
         launch_streamed();
-    } else if (two_stage && P.n_spheres <= 512) {
+    } else if (two_stage) {
         ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsS<512>> (two-stage, stage-1 triples in kernel parameter space)";
         auto* ps = reinterpret_cast<PS512*>(ctx->h_params.data());
         fill_s(ps);
         k_s512<<<sms * 4, VT, smem_v, st>>>(*ps);
-    } else if (two_stage) {
-        ctx->last_kernel = "k_trace_paths_v<256,4,2,8,TraceParamsS<768>> (two-stage, stage-1 triples in kernel parameter space)";
-        auto* ps = reinterpret_cast<PS768*>(ctx->h_params.data());
-        fill_s(ps);
-        k_s768<<<sms * 4, VT, smem_v, st>>>(*ps);
     } else if (two_stage_smem) {
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
