@@ -395,7 +395,18 @@ __device__ __forceinline__ void walk_next(uint32_t maddr, uint32_t stride_bytes,
 // out of the uniform datapath, LDC into vector registers instead of LDCU, and the sweep drops to 74 % issue-slot use: C2
 // 54.9 ms), out of line in the kernels that read stage 1 from shared memory (no uniform operands to lose, and the walk
 // loop stays small: C4 460 vs 472 ms inline, 785 spheres 12.04 vs 12.37 ms).
-constexpr uint32_t PEND_EMPTY = 1u, PEND_FULL = 1u << 27;
+constexpr uint32_t PEND_EMPTY = 1u;
+// CB = blocks per chunk (8 or 16): an entry is the sphere index within the chunk (8 or 9 bits) + the ray bit
+template <int CB> struct Pend { static constexpr int index_bits = CB == 16 ? 9 : 8, entry_bits = index_bits + 1; static constexpr uint32_t full = 1u << (3 * entry_bits); };
+// Chunk size of k_trace_paths_l: 16 blocks (512 spheres).  A walk runs as many steps as the fullest lane of the warp holds
+// candidates; over a chunk twice as long the lanes' counts even out and half as many walks are set up (10 001 spheres: 20 chunks
+// instead of 40): C4 424.1 -> 420.5 ms, 785 / 1 297 / 2 501 spheres 11.18 / 16.98 / 29.45 -> 10.77 / 16.26 / 28.26.  Its 16 mask
+// words per ray (82 KB at 640 threads) fit beside the stage-1 data; the parameter-space kernels (four CTAs' path state per SM) and
+// the streamed kernel (per-warp double buffers) have room for 8.
+#ifndef RTB_L_CHUNK
+#define RTB_L_CHUNK 16
+#endif
+constexpr int L_CHUNK_BLOCKS = RTB_L_CHUNK;
 
 __device__ __noinline__ Best stage3_now(ExactRay ray32, double4 sphere, int idx, Best best) {
     test_candidate(promote_ray(ray32), ray32.both_roots, sphere, idx, best.t, best.i);
@@ -420,7 +431,7 @@ __device__ __forceinline__ float slab_value_packed(const SlabRay& s, float ca, f
 }
 
 // Stage 2 of the two-stage sweep for ray r and one chunk: the lane-parallel walk over its stage-1 candidates.
-template <bool CALL_OVERFLOW, class RaySrc>
+template <bool CALL_OVERFLOW, int CB, class RaySrc>
 __device__ RTB_REFINE_INLINE void refine_chunk(const uint32_t* masks_r, int stride, uint32_t todo, int first_sphere,
                                           const float4* __restrict__ g_filter, const double4* __restrict__ g_exact, float h_bound, FilterRay f,
                                           const RaySrc& rays, int r, uint32_t& pend, Best& best) {
@@ -446,7 +457,7 @@ __device__ RTB_REFINE_INLINE void refine_chunk(const uint32_t* masks_r, int stri
         float h;
         const float q = filter_value_packed(f, fs, h);                                             // stage 2 (FP32, conservative)
         if (!(__float_as_uint(q) >> 31) && !(h < h_min)) {
-            if (pend < PEND_FULL) pend = ((pend << 9) + (uint32_t)(r << 8)) | ((uint32_t)idx & 255u);   // park it for drain_pending (chunks start at multiples of 256)
+            if (pend < Pend<CB>::full) pend = ((pend << Pend<CB>::entry_bits) + (uint32_t)(r << Pend<CB>::index_bits)) | ((uint32_t)idx & ((1u << Pend<CB>::index_bits) - 1u));   // park it for drain_pending (chunks start at multiples of their size)
             else if (CALL_OVERFLOW) best = stage3_now(rays.load(r), load_exact(&g_exact[idx]), idx, best);   // the lane's fourth: now
             else test_candidate(promote_ray(rays.load(r)), rays.both_roots(), load_exact(&g_exact[idx]), idx, best.t, best.i);
         }
@@ -455,14 +466,14 @@ __device__ RTB_REFINE_INLINE void refine_chunk(const uint32_t* masks_r, int stri
 
 // Stage 3 (f64, exact) for the parked survivors of all RAYS rays of the lane: one pass per entry of the fullest lane.  The
 // ray is fetched and promoted HERE, so that nothing of it is live across the walks (the kernels run at the 64-register limit).
-template <int RAYS, class RaySrc>
+template <int RAYS, int CB, class RaySrc>
 __device__ __forceinline__ void drain_pending(uint32_t pend, int first_sphere, const double4* __restrict__ g_exact, const RaySrc& rays,
                                               double (&best_t)[RAYS], int (&best_i)[RAYS]) {
     static_assert(RAYS <= 2, "a pending entry has one ray bit");
     while (pend != PEND_EMPTY) {
-        const uint32_t e = pend & 511u;
-        pend >>= 9;
-        const int r = (int)(e >> 8), idx = first_sphere + (int)(e & 255u);
+        const uint32_t e = pend & ((1u << Pend<CB>::entry_bits) - 1u);
+        pend >>= Pend<CB>::entry_bits;
+        const int r = (int)(e >> Pend<CB>::index_bits), idx = first_sphere + (int)(e & ((1u << Pend<CB>::index_bits) - 1u));
         const ExactRay ray32 = rays.load(r);
         double bt = best_t[0];
         int bi = best_i[0];
@@ -563,7 +574,7 @@ struct SmemSlab {
     }
 };
 
-template <int RAYS, class S1, class RaySrc>
+template <int RAYS, int CB, class S1, class RaySrc>
 __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays, const float4* __restrict__ g_filter,
                                                 const double4* __restrict__ g_exact, float h_bound, int count, uint32_t* masks, int stride,
                                                 const SlabRay (&sl)[RAYS], const FilterRay (&f)[RAYS], double (&best_t)[RAYS], int (&best_i)[RAYS]) {
@@ -571,8 +582,8 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
     // groups of 8 spheres that exist in the scene's last block; 1..3: that block takes the short path (S1::partial)
     const int tail_groups = ((count & (SWEEP_BLOCK - 1)) + 7) >> 3;
     const bool short_tail = tail_groups >= 1 && tail_groups <= S1::max_tail_groups;
-    for (int cb = 0; cb < n_blocks; cb += 8) {
-        const int nb = n_blocks - cb < 8 ? n_blocks - cb : 8;
+    for (int cb = 0; cb < n_blocks; cb += CB) {
+        const int nb = n_blocks - cb < CB ? n_blocks - cb : CB;
         const bool tail_here = short_tail && cb + nb == n_blocks;
         const int nb_full = tail_here ? nb - 1 : nb;
         uint32_t todo[RAYS];
@@ -588,7 +599,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
             s1.template block<RAYS>(cb + b, sl, mask);
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
-                masks[(r * 8 + b) * stride] = mask[r];
+                masks[(r * CB + b) * stride] = mask[r];
                 todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
             }
         }
@@ -599,7 +610,7 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
             s1.template partial<RAYS>(cb + nb_full, tail_groups, sl, mask);
 #pragma unroll
             for (int r = 0; r < RAYS; r++) {
-                masks[(r * 8 + nb_full) * stride] = mask[r];
+                masks[(r * CB + nb_full) * stride] = mask[r];
                 todo[r] |= mask[r] != 0xffffffffu ? bit : 0u;
             }
         }
@@ -608,11 +619,11 @@ __device__ __forceinline__ void sweep_two_stage(const S1& s1, const RaySrc& rays
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {
             Best bst{best_t[r], best_i[r]};
-            refine_chunk<S1::overflow_by_call>(masks + r * 8 * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
+            refine_chunk<S1::overflow_by_call, CB>(masks + r * CB * stride, stride, todo[r], cb * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
-        drain_pending<RAYS>(pend, cb * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
+        drain_pending<RAYS, CB>(pend, cb * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
     }
 }
 
@@ -675,11 +686,11 @@ __device__ __forceinline__ void sweep_two_stage_stream(float4* wbuf, const float
 #pragma unroll
         for (int r = 0; r < RAYS; r++) {                      // ---- stages 2 and 3 ----
             Best bst{best_t[r], best_i[r]};
-            refine_chunk<true>(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
+            refine_chunk<true, 8>(masks + r * 8 * stride, stride, todo[r], c * 8 * SWEEP_BLOCK, g_filter, g_exact, h_bound, f[r], rays, r, pend, bst);
             best_t[r] = bst.t;
             best_i[r] = bst.i;
         }
-        drain_pending<RAYS>(pend, c * 8 * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
+        drain_pending<RAYS, 8>(pend, c * 8 * SWEEP_BLOCK, g_exact, rays, best_t, best_i);
     }
     cp_async_wait<0>();
 }
@@ -1112,13 +1123,13 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths(const Trace
 // slots in REGISTERS (one CTA per SM has registers to spare: 65536 / THREADS per thread), so that shared memory holds
 // only the triples and the stage-1 masks and THREADS can be larger than in the shared-state variant: more warps to hide
 // the refine walks, whose sphere records come from L2 here (the L1 is all but given to shared memory).
-// dynamic smem: 8 * RAYS * THREADS mask words + n_padded * 3 floats.
+// dynamic smem: L_CHUNK_BLOCKS * RAYS * THREADS mask words + n_padded * 3 floats.
 template <int THREADS, int RAYS, bool STRIDED>
 __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_constant__ TraceParamsL PV) {
     const TraceParams& P = PV.b;
     extern __shared__ float4 smem4[];
     uint32_t* masks = reinterpret_cast<uint32_t*>(smem4) + threadIdx.x;
-    float4* s_slab = smem4 + 8 * RAYS * THREADS / 4;
+    float4* s_slab = smem4 + L_CHUNK_BLOCKS * RAYS * THREADS / 4;
     {
         const int n4 = PV.n_padded * 3 / 4;
         for (int i = threadIdx.x; i < n4; i += THREADS) s_slab[i] = __ldg(&PV.s1[i]);
@@ -1163,7 +1174,7 @@ __global__ void __launch_bounds__(THREADS, 1) k_trace_paths_l(const __grid_const
             bt[r] = RTB_INF_D;
             best_i[r] = -1;
         }
-        sweep_two_stage<RAYS>(SmemSlab{s_slab}, RegisterRays{ray}, P.filter, P.exact, P.h_bound, P.n_spheres, masks, THREADS, slab, flt, bt, best_i);
+        sweep_two_stage<RAYS, L_CHUNK_BLOCKS>(SmemSlab{s_slab}, RegisterRays{ray}, P.filter, P.exact, P.h_bound, P.n_spheres, masks, THREADS, slab, flt, bt, best_i);
 #pragma unroll
         for (int r = 0; r < RAYS; r++) best_t[r] = __double2float_rn(bt[r]);
         swept = true;
@@ -1335,9 +1346,9 @@ __global__ void __launch_bounds__(THREADS, MIN_BLOCKS) k_trace_paths_v(const __g
             for (int r = 0; r < RAYS; r++)
                 slab[r] = make_slab_ray(F(0, r), F(1, r), F(2, r), F(3, r), F(4, r), F(5, r), plen2_3(mk3(F(3, r), F(4, r), F(5, r))), PV.up_axis, PV.rp_min);
             if constexpr (PV_T::s1_smem)
-                sweep_two_stage<RAYS>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
+                sweep_two_stage<RAYS, 8>(SmemSlab{s_slab}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab, flt, best_t, best_i);
             else
-                sweep_two_stage<RAYS>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab,
+                sweep_two_stage<RAYS, 8>(ParamSlab<PV_T>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.filter, P.exact, P.h_bound, P.n_spheres, list, THREADS, slab,
                                       flt, best_t, best_i);
         } else {
             sweep_spheres_bitmap<RAYS, CAP>(ParamSpheres<PV_T::capacity>{PV}, SmemRays<RAYS, THREADS>{st, P.both_roots != 0}, P.exact, P.n_spheres, list, THREADS,

@@ -322,7 +322,7 @@ int launch_trace(rtb200_ctx* ctx, const rtb200_camera* cam, const rtb200_params*
         rtb::TraceParamsL pl;
         std::memset(&pl, 0, sizeof pl);
         pl.b = P; pl.up_axis = ctx->up_axis; pl.rp_min = ctx->slab_rp_min; pl.n_padded = ctx->n_padded; pl.s1 = ctx->d_slabq;
-        const size_t smem_slr = (size_t)8 * LR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
+        const size_t smem_slr = (size_t)rtb::L_CHUNK_BLOCKS * LR * LRT * sizeof(uint32_t) + (size_t)ctx->n_padded * 3 * sizeof(float);
         if (smem_slr <= ctx->max_optin_smem && !(p->flags & RTB200_FLAG_SHARED_STATE)) {
             ctx->last_kernel = "k_trace_paths_l<640,2> (two-stage, stage-1 triples staged in shared memory, path state in registers)";
             k_slr<<<sms, LRT, smem_slr, st>>>(pl);
