@@ -90,10 +90,10 @@ typedef struct rtb200_params {
 #define RTB200_FLAG_RAYS2 2 /* force the two-slots-per-lane trace kernels                                                  */
 #define RTB200_FLAG_ONE_STAGE 4 /* all pairs through the 8-instruction filter (no slab stage)                               */
 #define RTB200_FLAG_TWO_STAGE 8 /* force the slab stage (3-FFMA all-pairs test, then filter, then the exact arithmetic) even
-                                   where the scene layout does not favour it; <= 768 spheres from parameter space, beyond
+                                   where the scene layout does not favour it; <= 512 spheres from parameter space, beyond
                                    that from shared memory                                                              */
 
-#define RTB200_FLAG_SHARED_STATE 32 /* scenes beyond 768 spheres, two-stage sweep: keep the path state in shared memory (512
+#define RTB200_FLAG_SHARED_STATE 32 /* scenes beyond 512 spheres, two-stage sweep: keep the path state in shared memory (512
                                       threads per SM) instead of registers (640 threads per SM, the default)            */
 
 #define RTB200_FLAG_STREAMED 64 /* force the streamed two-stage kernel: stage-1 data fetched per warp from global memory
