@@ -389,8 +389,8 @@ __device__ __forceinline__ void walk_next(uint32_t maddr, uint32_t stride_bytes,
 // Stage-2 survivors are not tested on the spot: a lane parks them in ONE register and the warp runs stage 3 once per
 // chunk for the survivors of all its rays together (drain_pending).  On the spot, stage 3 ran with ~6 of 32 lanes active,
 // 1.5 times per ray and chunk; deferred, the same lane-tests take ~1.7 passes per chunk for both rays.  The order is free
-// (test_candidate's rule).  pend = a stack of 9-bit entries (ray << 8 | sphere index within the chunk) above a sentinel 1:
-// empty = 1, three entries fill it; a fourth survivor of one lane in one chunk (rare) is tested on the spot — inline in the
+// (test_candidate's rule).  pend = a stack of 9-bit entries (ray << 8 | sphere index within the chunk; 10 bits in the 16-block
+// chunks of k_trace_paths_l, Pend<CB>) above a sentinel 1: empty = 1, three entries fill it; a fourth survivor of one lane in one chunk (rare) is tested on the spot — inline in the
 // parameter-space kernels (with a CALL inside the chunk loop ptxas moves the loop's counters and the stage-1 sphere operands
 // out of the uniform datapath, LDC into vector registers instead of LDCU, and the sweep drops to 74 % issue-slot use: C2
 // 54.9 ms), out of line in the kernels that read stage 1 from shared memory (no uniform operands to lose, and the walk
